@@ -1,0 +1,30 @@
+// host.h — host-side declarations shared by the C-ABI translation units.
+#pragma once
+#include "esb_params.h"
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace esb {
+
+struct LoadedPreset {
+    EsbEngineParams params;
+    std::string name;
+    std::vector<std::string> irFiles; // per exhaust system, normalised to "sound-library/..."
+};
+
+// preset.cpp
+void parsePreset(const std::string &jsonText, LoadedPreset &out);
+void loadPresetFile(const std::string &path, LoadedPreset &out);
+
+// wav.cpp — 16-bit PCM RIFF reader/writer (replaces dr_wav, wav_loader.h:41-63)
+struct WavData {
+    int sampleRate = 0;
+    int channels = 0;
+    std::vector<int16_t> samples; // interleaved
+};
+bool readWav(const std::string &path, WavData &out, std::string &err);
+bool writeWavMono16(const std::string &path, const int16_t *samples, size_t n, int sampleRate, std::string &err);
+
+} // namespace esb
