@@ -113,8 +113,10 @@ ESB_HD double esb_log(double x) {
 }
 
 /* ---- exp --------------------------------------------------------------- */
-/* |x| < 700. */
+/* Flushes to 0 below -700 and saturates above 700 (no subnormal results). */
 ESB_HD double esb_exp(double x) {
+    if (x < -700.0) return 0.0;
+    if (x > 700.0) x = 700.0;
     const double LN2_HI = 6.93147180369123816490e-01;
     const double LN2_LO = 1.90821492927058770002e-10;
     const double INV_LN2 = 1.44269504088896338700e+00;
