@@ -1,6 +1,7 @@
 // host.h — host-side declarations shared by the C-ABI translation units.
 #pragma once
 #include "esb_params.h"
+#include "esb_device.h"
 
 #include <cstdint>
 #include <string>
@@ -26,5 +27,11 @@ struct WavData {
 };
 bool readWav(const std::string &path, WavData &out, std::string &err);
 bool writeWavMono16(const std::string &path, const int16_t *samples, size_t n, int sampleRate, std::string &err);
+
+// instance_init.cpp — derived constants and the initial state column of an instance
+int lanesForCylinders(int n);
+void deriveDeviceParams(const EsbEngineParams &P, double simFreq, int fluidSteps, int maxIterations, double minDelta, double beta,
+                        uint64_t seedBase, EsbDeviceParams &D);
+void initialStateColumn(const EsbDeviceParams &D, std::vector<double> &col);
 
 } // namespace esb
