@@ -79,5 +79,8 @@ struct EsbPostArgs {
 };
 cudaError_t esbLaunchSynthPost(const EsbPostArgs &a, cudaStream_t stream);
 
+// SineSimulator input (synth_kernels.cu)
+cudaError_t esbLaunchSine(double *stream, int nSteps, int channels, int nInst, const double *ctl, double *phase, double simFreq, cudaStream_t st);
+
 // FP32 / FP64 pipe peak probes (peak_probe.cu): register-resident FMA loops, returns ops issued
 cudaError_t esbLaunchPeakProbe(int fp64, int fma, int blocks, int threads, int iters, float *sink, cudaStream_t stream);
