@@ -71,6 +71,9 @@ void Batch::release() {
     auto fr = [](auto *&p) { if (p) { cudaFree(p); p = nullptr; } };
     fr(dD); fr(dS); fr(dCtl); fr(dKeyStep); fr(dKeyThr); fr(dKeyDyno); fr(dStream); fr(dChanState); fr(dChanLast); fr(dInstState);
     fr(dX); fr(dHr); fr(dY); fr(dPcm); fr(dPcmFloat); fr(dTel); fr(dSinePhase);
+    for (auto &t : timed) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
+    for (auto e : eventPool) cudaEventDestroy(e);
+    timed.clear(); eventPool.clear();
     if (ownStream && stream) { cudaStreamDestroy(stream); stream = nullptr; }
 }
 
@@ -353,7 +356,9 @@ int Batch::advanceChunk(int nSteps, double *telDev, int telEvery, long long telB
         a.D = dD; a.S = dS; a.ctl = dCtl; a.nInst = nInst; a.nSteps = nSteps; a.stepBase = stepCount;
         a.nKeys = nKeys; a.keyStep = dKeyStep; a.keyThrottle = dKeyThr; a.keyDynoSpeed = dKeyDyno;
         a.stream = dStream; a.channels = channels; a.telemetry = telDev; a.telemetryEvery = telEvery; a.telemetryBase = telBase;
+        markBegin(0);
         ESB_CUDA(esbLaunchPhysics(a, lanes, blockThreads, stream));
+        markEnd();
         ++launchCounts[0];
     }
     lastStreamSteps = nSteps;
@@ -378,7 +383,9 @@ int Batch::advanceChunk(int nSteps, double *telDev, int telEvery, long long telB
         a.stream = dStream; a.nSteps = nSteps; a.channels = channels; a.nInst = nInst; a.nInstPad = nInstPad;
         a.clock = before; a.chanState = dChanState; a.chanLast = dChanLast; a.sampleBase = P;
         a.X = dX; a.xStride = xStride; a.hist = hist; a.xOrigin = xOrigin; a.seedBase = cfg.seed; a.sp = sp;
+        markBegin(1);
         ESB_CUDA(esbLaunchSynthPre(a, stream));
+        markEnd();
         ++launchCounts[1];
     }
     if (m > 0) {
@@ -387,18 +394,51 @@ int Batch::advanceChunk(int nSteps, double *telDev, int telEvery, long long telB
         f.X = dX; f.xStride = xStride; f.hist = hist; f.xOrigin = xOrigin; f.hr = dHr; f.Lp = Lp;
         f.rows = channels * nInstPad; f.rowsPerIr = nInstPad; f.nIr = channels; f.n0 = n0; f.count = (int)(P + m - n0);
         f.Y = dY; f.yStride = yStride;
+        markBegin(2);
         ESB_CUDA(esbLaunchFir(f, stream));
+        markEnd();
         ++launchCounts[2];
         EsbPostArgs q;
         q.X = dX; q.xStride = xStride; q.hist = hist; q.xOrigin = xOrigin; q.Y = dY; q.yStride = yStride; q.n0 = n0;
         q.channels = channels; q.nInst = nInst; q.nInstPad = nInstPad; q.first = P; q.count = (int)m;
         q.instState = dInstState; q.pcm = dPcm; q.pcmFloat = wantPcmFloat ? dPcmFloat : nullptr;
         q.pcmStride = pcmStride; q.pcmOrigin = pcmOrigin; q.sp = sp;
+        markBegin(3);
         ESB_CUDA(esbLaunchSynthPost(q, stream));
+        markEnd();
         ++launchCounts[3];
     }
     samplesProduced += m;
     stepCount += nSteps;
+    return ESIM_SUCCESS;
+}
+
+cudaEvent_t Batch::takeEvent() {
+    if (!eventPool.empty()) { cudaEvent_t e = eventPool.back(); eventPool.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+}
+void Batch::markBegin(int cls) {
+    if (!profiling) return;
+    TimedLaunch t{cls, takeEvent(), takeEvent()};
+    cudaEventRecord(t.a, stream);
+    timed.push_back(t);
+}
+void Batch::markEnd() {
+    if (!profiling || timed.empty()) return;
+    cudaEventRecord(timed.back().b, stream);
+}
+int Batch::kernelTimes(double ms[4], long long launches[4]) {
+    if (device >= 0) ESB_CUDA(cudaSetDevice(device));
+    if (stream) ESB_CUDA(cudaStreamSynchronize(stream));
+    for (auto &t : timed) {
+        float e = 0;
+        if (cudaEventElapsedTime(&e, t.a, t.b) == cudaSuccess) { accMs[t.cls] += e; ++accLaunches[t.cls]; }
+        eventPool.push_back(t.a); eventPool.push_back(t.b);
+    }
+    timed.clear();
+    for (int i = 0; i < 4; ++i) { ms[i] = accMs[i]; launches[i] = accLaunches[i]; accMs[i] = 0; accLaunches[i] = 0; }
     return ESIM_SUCCESS;
 }
 

@@ -34,6 +34,9 @@ class Batch {
     int getLastStream(double *out, int maxSteps, int *outSteps);
     int getStats(int inst, EngineSimStats *out);
     int writeWavs(const char *dir, const char *prefix);
+    // per-kernel-class CUDA-event timing (physics, synth-pre, fir, synth-post) for the roofline lines of bench.py
+    void setProfiling(bool on) { profiling = on; }
+    int kernelTimes(double ms[4], long long launches[4]);
 
     std::string lastError;
     EngineSimConfig cfg{};
@@ -76,6 +79,15 @@ class Batch {
     long long hist = 0, xStride = 0, xOrigin = 0, xCapSamples = 0, yStride = 0, chunkSamplesMax = 0;
     size_t telBytes = 0;
     EsbSynthClock clock{};
+    struct TimedLaunch { int cls; cudaEvent_t a, b; };
+    bool profiling = false;
+    std::vector<TimedLaunch> timed;
+    std::vector<cudaEvent_t> eventPool;
+    double accMs[4] = {0, 0, 0, 0};
+    long long accLaunches[4] = {0, 0, 0, 0};
+    cudaEvent_t takeEvent();
+    void markBegin(int cls);
+    void markEnd();
 };
 
 } // namespace esb

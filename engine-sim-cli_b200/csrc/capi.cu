@@ -150,6 +150,15 @@ int32_t EsbBatchGetLaunchCounts(EsbBatchHandle h, int64_t counts[4]) {
     return ESIM_SUCCESS;
 }
 
+int32_t EsbBatchSetProfiling(EsbBatchHandle h, int32_t on) { if (!h) return ESIM_ERROR_INVALID_HANDLE; h->b.setProfiling(on != 0); return ESIM_SUCCESS; }
+int32_t EsbBatchGetKernelTimes(EsbBatchHandle h, double ms[4], int64_t launches[4]) {
+    if (!h) return ESIM_ERROR_INVALID_HANDLE;
+    long long l[4];
+    const int rc = h->b.kernelTimes(ms, l);
+    for (int i = 0; i < 4; ++i) launches[i] = l[i];
+    return rc;
+}
+
 int32_t EsbFirRun(const float *dX, int64_t xStride, int64_t hist, const float *dHr, int32_t Lp, int32_t nIr, int32_t rowsPerIr, int32_t rows,
                   int64_t count, float *dY, int64_t yStride, void *cudaStream) {
     if (!dX || !dHr || !dY || count <= 0) return ESIM_ERROR_INVALID_PARAMETER;

@@ -150,6 +150,11 @@ int32_t EsbBatchSetLaunchConfig(EsbBatchHandle b, int32_t blockThreads, int32_t 
 /* Kernel launches issued so far by this batch (physics, synth-pre, fir, synth-post) */
 int32_t EsbBatchGetLaunchCounts(EsbBatchHandle b, int64_t counts[4]);
 
+/* CUDA-event timing of each kernel class (physics, synth-pre, fir, synth-post): accumulated milliseconds and
+ * launch counts since the last query (the query synchronises the batch's stream and resets the sums). */
+int32_t EsbBatchSetProfiling(EsbBatchHandle b, int32_t enabled);
+int32_t EsbBatchGetKernelTimes(EsbBatchHandle b, double ms[4], int64_t launches[4]);
+
 /* Stand-alone convolution (BASELINE config 5): y[c][n] = sum_k h[k] x[c][n-k], zero history.
  * All pointers are DEVICE pointers; x: [channels][xStride] with 'lead' zero floats before sample 0 ...
  * see engine-sim-cli_b200/fir.py for the layout helper. */
