@@ -179,7 +179,9 @@ def b200_main(args, rank, world, local_rank):
     blob, ir = load_workload()
     n = args.instances
     steps = int(round(args.sim_seconds * SIM_FREQ))
-    stream = torch.cuda.current_stream().cuda_stream
+    side = torch.cuda.Stream()          # a non-default stream: the library launches on it and the events below see it
+    torch.cuda.set_stream(side)
+    stream = side.cuda_stream
     b = esb.BatchSimulator(n, device=local_rank, sim_freq=SIM_FREQ, seed=rank * n, stream=stream)
     b.load_params(blob)
     taps = [b.set_impulse_response(c, ir, 0.001) for c in range(2)]

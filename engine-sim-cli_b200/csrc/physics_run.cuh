@@ -77,8 +77,8 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, const Group<G> &g) {
     s.clutchTorque = S[(size_t)ESB_GF_CLUTCH_TORQUE * n + inst];
     s.lastIter = (int)S[(size_t)ESB_GF_LAST_ITER * n + inst];
     s.totalExhaustFlow = S[(size_t)ESB_GF_TOTAL_EXH_FLOW * n + inst];
-    loadCell(s.plenum, S, n, (size_t)(ESB_GF_PLENUM + 8 * k.inIdx) * n + inst);
-    loadCell(s.collector, S, n, (size_t)(ESB_GF_COLLECTOR + 8 * k.exIdx) * n + inst);
+    loadCell(s.plenum, S, n, (size_t)(ESB_GF_PLENUM + 8 * k.shIn) * n + inst);
+    loadCell(s.collector, S, n, (size_t)(ESB_GF_COLLECTOR + 8 * k.shEx) * n + inst);
     loadBody(s.piston, S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_PISTON, cyl) * n + inst);
     loadBody(s.rod, S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_ROD, cyl) * n + inst);
     for (int r = 0; r < 5; ++r) s.lam[r] = S[(size_t)ESB_CYL_FIELD(ESB_CF_LAMBDA + r, cyl) * n + inst];
@@ -129,12 +129,13 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, const Group<G> &g) {
         }
         if (sample) {
             const double p0 = g.bcast(cellPressure(s.chamber), 0);
+            const double pMan = g.bcast(cellPressure(s.plenum), k.plen0Lane);
             if (g.lane == 0) {
                 const long long idx = (gstep + 1) / a.telemetryEvery - 1 - a.telemetryBase;
                 double *t = a.telemetry + (size_t)idx * ESB_TELEMETRY_STRIDE * n + inst;
                 t[0 * n] = -s.crank.w * (30.0 / kPi);
                 t[1 * n] = s.dynoTorque;
-                t[2 * n] = cellPressure(s.plenum);
+                t[2 * n] = pMan;
                 t[3 * n] = s.totalExhaustFlow;
                 t[4 * n] = p0;
                 t[5 * n] = cycleAngle(s.crank, D->P.tdc);
@@ -160,7 +161,10 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, const Group<G> &g) {
         S[(size_t)ESB_GF_LAST_ITER * n + inst] = (double)s.lastIter;
         S[(size_t)ESB_GF_TOTAL_EXH_FLOW * n + inst] = s.totalExhaustFlow;
     }
-    if (k.active) {
+    if (k.chainMode) {
+        if (k.roleP) storeCell(s.plenum, S, n, (size_t)(ESB_GF_PLENUM + 8 * k.shIn) * n + inst);
+        if (k.roleC) storeCell(s.collector, S, n, (size_t)(ESB_GF_COLLECTOR + 8 * k.shEx) * n + inst);
+    } else if (k.active) {
         // the first cylinder plumbed to an intake / exhaust system stores that replica
         const EsbEngineParams &P = D->P;
         bool firstIn = true, firstEx = true;
@@ -170,6 +174,8 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, const Group<G> &g) {
         }
         if (firstIn) storeCell(s.plenum, S, n, (size_t)(ESB_GF_PLENUM + 8 * k.inIdx) * n + inst);
         if (firstEx) storeCell(s.collector, S, n, (size_t)(ESB_GF_COLLECTOR + 8 * k.exIdx) * n + inst);
+    }
+    if (k.active) {
         storeBody(s.piston, S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_PISTON, cyl) * n + inst);
         storeBody(s.rod, S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_ROD, cyl) * n + inst);
         for (int r = 0; r < 5; ++r) S[(size_t)ESB_CYL_FIELD(ESB_CF_LAMBDA + r, cyl) * n + inst] = s.lam[r];
