@@ -63,7 +63,7 @@ def lib():
             "EsbBatchGetDevicePcm": [vp, C.POINTER(vp), C.POINTER(i64), C.POINTER(i32)], "EsbBatchGetState": [vp, vp, C.POINTER(i32)],
             "EsbBatchGetLastStream": [vp, vp, i32, C.POINTER(i32)], "EsbBatchGetStats": [vp, i32, vp], "EsbBatchWriteWavs": [vp, C.c_char_p, C.c_char_p],
             "EsbBatchSetLaunchConfig": [vp, i32, i32], "EsbBatchGetLaunchCounts": [vp, vp],
-            "EsbBatchSetProfiling": [vp, i32], "EsbBatchGetKernelTimes": [vp, vp, vp],
+            "EsbBatchSetProfiling": [vp, i32], "EsbBatchSetPhysicsShape": [vp, i32, i32], "EsbBatchGetKernelTimes": [vp, vp, vp],
             "EsbFirRun": [vp, i64, i64, vp, i32, i32, i32, i32, i64, vp, i64, vp], "EsbProbePeak": [i32, i32, C.POINTER(dbl)],
             "EngineSimCreate": [vp, C.POINTER(vp)], "EngineSimLoadScript": [vp, C.c_char_p, C.c_char_p], "EngineSimLoadParams": [vp, vp, vp, i32, flt],
             "EngineSimDestroy": [vp], "EngineSimSetThrottle": [vp, dbl], "EngineSimSetSpeedControl": [vp, dbl], "EngineSimSetIgnition": [vp, i32],
@@ -241,6 +241,9 @@ class BatchSimulator:
 
     def write_wavs(self, directory, prefix="engine_"):
         self._check(lib().EsbBatchWriteWavs(self.h, directory.encode(), prefix.encode()))
+
+    def set_physics_shape(self, inst_per_warp=0, variant=0):
+        self._check(lib().EsbBatchSetPhysicsShape(self.h, inst_per_warp, variant))
 
     def set_profiling(self, on=True):
         self._check(lib().EsbBatchSetProfiling(self.h, int(on)))

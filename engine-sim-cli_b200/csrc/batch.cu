@@ -321,7 +321,7 @@ int Batch::setSchedule(int nk, const int64_t *keyStep, const double *thr, const 
 
 int Batch::setLaunchConfig(int blockThreads_, int stepsPerLaunch_) {
     if (blockThreads_ > 0) {
-        if (blockThreads_ % 32 != 0 || blockThreads_ > 128) { lastError = "blockThreads must be 32, 64, 96 or 128"; return ESIM_ERROR_INVALID_PARAMETER; }
+        if (blockThreads_ % 32 != 0 || blockThreads_ > 256) { lastError = "blockThreads must be a multiple of 32, at most 256"; return ESIM_ERROR_INVALID_PARAMETER; }
         blockThreads = blockThreads_;
     }
     if (stepsPerLaunch_ > 0 && stepsPerLaunch_ != stepsPerLaunch) {
@@ -357,7 +357,7 @@ int Batch::advanceChunk(int nSteps, double *telDev, int telEvery, long long telB
         a.nKeys = nKeys; a.keyStep = dKeyStep; a.keyThrottle = dKeyThr; a.keyDynoSpeed = dKeyDyno;
         a.stream = dStream; a.channels = channels; a.telemetry = telDev; a.telemetryEvery = telEvery; a.telemetryBase = telBase;
         markBegin(0);
-        ESB_CUDA(esbLaunchPhysics(a, lanes, blockThreads, stream));
+        ESB_CUDA(esbLaunchPhysics(a, lanes, blockThreads, instPerWarp, kernelVariant, stream));
         markEnd();
         ++launchCounts[0];
     }

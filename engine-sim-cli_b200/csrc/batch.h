@@ -45,6 +45,7 @@ class Batch {
     bool loaded = false, sineMode = false;
     int device = -1, nInst = 0, nInstPad = 0, channels = 0, lanes = 8;
     double simFreq = 10000.0;
+    int instPerWarp = 0, kernelVariant = 0; // physics launch shape (0 = full warps, 255-register build)
     int solverMaxIt = 24;
     double solverMinDelta = 1e-7, solverBeta = 0.2;
     std::vector<std::vector<float>> irs;
@@ -68,7 +69,7 @@ class Batch {
     EsbSynthParams synthParams() const;
 
     bool ownStream = false, ctlDirty = false, wantPcmFloat = false;
-    int blockThreads = 64, stepsPerLaunch = 668;
+    int blockThreads = 128, stepsPerLaunch = 668;
     EsbDeviceParams hostD{};
     EsbDeviceParams *dD = nullptr;
     double *dS = nullptr, *dCtl = nullptr, *dKeyThr = nullptr, *dKeyDyno = nullptr, *dStream = nullptr, *dChanLast = nullptr, *dTel = nullptr, *dSinePhase = nullptr;

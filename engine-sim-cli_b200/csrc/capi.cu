@@ -144,6 +144,12 @@ int32_t EsbBatchWriteWavs(EsbBatchHandle h, const char *dir, const char *prefix)
     return h->b.writeWavs(dir, prefix);
 }
 int32_t EsbBatchSetLaunchConfig(EsbBatchHandle h, int32_t bt, int32_t spl) { return h ? h->b.setLaunchConfig(bt, spl) : ESIM_ERROR_INVALID_HANDLE; }
+int32_t EsbBatchSetPhysicsShape(EsbBatchHandle h, int32_t instPerWarp, int32_t variant) {
+    if (!h) return ESIM_ERROR_INVALID_HANDLE;
+    if (instPerWarp < 0 || variant < 0 || variant > 2) { h->b.lastError = "invalid physics launch shape"; return ESIM_ERROR_INVALID_PARAMETER; }
+    h->b.instPerWarp = instPerWarp; h->b.kernelVariant = variant;
+    return ESIM_SUCCESS;
+}
 int32_t EsbBatchGetLaunchCounts(EsbBatchHandle h, int64_t counts[4]) {
     if (!h) return ESIM_ERROR_INVALID_HANDLE;
     for (int i = 0; i < 4; ++i) counts[i] = h->b.launchCounts[i];

@@ -6,7 +6,7 @@
 namespace esbk { struct RunArgs; }
 
 // K1+K2: physics (physics_kernel.cu)
-cudaError_t esbLaunchPhysics(const esbk::RunArgs &a, int lanes, int blockThreads, cudaStream_t stream);
+cudaError_t esbLaunchPhysics(const esbk::RunArgs &a, int lanes, int blockThreads, int instPerWarp, int variant, cudaStream_t stream);
 
 // Synthesizer clock: the 10 kHz -> 44.1 kHz resampler bookkeeping of Synthesizer::writeInput
 // (archive/PHYSICS_ANALYSIS.md:39-55), identical for every instance, so the host tracks it.

@@ -10,30 +10,49 @@
 
 namespace esbk {
 
-template <int G>
-__global__ void __launch_bounds__(128) esb_physics_kernel(RunArgs a) {
-    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
-    const int inst = tid / G;
-    if (inst >= a.nInst) return; // groups are lane-aligned, so a whole group leaves together
-    Group<G> g;
-    g.lane = tid % G;
+// MINB = resident blocks of 64 threads the compiler must make room for: 4 -> up to 255 registers per
+// thread (8 warps / SM), 7 -> 146, 8 -> 128 (16 warps / SM).  With instPerWarp < 32 / G the warps are
+// deliberately left part-empty: a batch too small to fill the machine is latency-bound, and more warps
+// hide more of the FP64 dependency latency than full warps do.
+template <int G, int MINB>
+__global__ void __launch_bounds__(256, (MINB >= 7 ? 2 : 1)) esb_physics_kernel(RunArgs a, int instPerWarp) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int laneInWarp = threadIdx.x & 31;
+    const int slot = laneInWarp / G;
+    // No thread leaves early (every thread of the block takes part in the lockstep barriers): lane groups
+    // without an instance of their own shadow the last instance and store nothing.
+    int inst = warp * instPerWarp + slot;
+    const bool live = slot < instPerWarp && inst < a.nInst;
+    if (!live) inst = a.nInst - 1;
+    Group<G> g;
+    g.lane = laneInWarp % G;
     g.mask = (G >= 32) ? 0xffffffffu : (((1u << G) - 1u) << (laneInWarp & ~(G - 1)));
-    runInstance<G>(a, inst, g);
+    runInstance<G>(a, inst, live, g);
 }
 
 } // namespace esbk
 
-cudaError_t esbLaunchPhysics(const esbk::RunArgs &a, int lanes, int blockThreads, cudaStream_t stream) {
-    const long long threads = (long long)a.nInst * lanes;
-    const int grid = (int)((threads + blockThreads - 1) / blockThreads);
+template <int G>
+static cudaError_t launchG(const esbk::RunArgs &a, int blockThreads, int instPerWarp, int variant, cudaStream_t stream) {
+    const int full = 32 / G;
+    if (instPerWarp <= 0 || instPerWarp > full) instPerWarp = full;
+    const long long warps = ((long long)a.nInst + instPerWarp - 1) / instPerWarp;
+    const int wpb = blockThreads / 32;
+    const int grid = (int)((warps + wpb - 1) / wpb);
+    if (G == 8 && variant == 1) esbk::esb_physics_kernel<G, (G == 8 ? 7 : 4)><<<grid, blockThreads, 0, stream>>>(a, instPerWarp);
+    else if (G == 8 && variant == 2) esbk::esb_physics_kernel<G, (G == 8 ? 8 : 4)><<<grid, blockThreads, 0, stream>>>(a, instPerWarp);
+    else esbk::esb_physics_kernel<G, 4><<<grid, blockThreads, 0, stream>>>(a, instPerWarp);
+    return cudaGetLastError();
+}
+
+cudaError_t esbLaunchPhysics(const esbk::RunArgs &a, int lanes, int blockThreads, int instPerWarp, int variant, cudaStream_t stream) {
+    if (blockThreads % 32 != 0 || blockThreads < 32 || blockThreads > 256) return cudaErrorInvalidValue;
     switch (lanes) {
-    case 1: esbk::esb_physics_kernel<1><<<grid, blockThreads, 0, stream>>>(a); break;
-    case 2: esbk::esb_physics_kernel<2><<<grid, blockThreads, 0, stream>>>(a); break;
-    case 4: esbk::esb_physics_kernel<4><<<grid, blockThreads, 0, stream>>>(a); break;
-    case 8: esbk::esb_physics_kernel<8><<<grid, blockThreads, 0, stream>>>(a); break;
-    case 16: esbk::esb_physics_kernel<16><<<grid, blockThreads, 0, stream>>>(a); break;
+    case 1: return launchG<1>(a, blockThreads, instPerWarp, variant, stream);
+    case 2: return launchG<2>(a, blockThreads, instPerWarp, variant, stream);
+    case 4: return launchG<4>(a, blockThreads, instPerWarp, variant, stream);
+    case 8: return launchG<8>(a, blockThreads, instPerWarp, variant, stream);
+    case 16: return launchG<16>(a, blockThreads, instPerWarp, variant, stream);
     default: return cudaErrorInvalidValue;
     }
-    return cudaGetLastError();
 }

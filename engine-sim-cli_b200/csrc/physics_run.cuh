@@ -56,7 +56,7 @@ ESB_DEV double scheduleValue(const long long *keyStep, const double *keyVal, int
 }
 
 template <int G>
-ESB_DEV void runInstance(const RunArgs &a, int inst, const Group<G> &g) {
+ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &g) {
     const EsbDeviceParams *D = a.D;
     const size_t n = (size_t)a.nInst;
     double *S = a.S;
@@ -121,16 +121,16 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, const Group<G> &g) {
         double out[ESB_MAX_EXHAUST];
         const double exhaustFlow = simulateStep<G>(s, k, D, ctl, g, seed, delayed, out, sample);
         if (k.active) {
-            ring[(size_t)s.delayPos * ringStride] = exhaustFlow;
+            if (live) ring[(size_t)s.delayPos * ringStride] = exhaustFlow;
             s.delayPos = (s.delayPos + 1 == k.delayLen) ? 0 : s.delayPos + 1;
         }
-        if (g.lane == 0) {
+        if (g.lane == 0 && live) {
             for (int c = 0; c < a.channels; ++c) a.stream[((size_t)step * a.channels + c) * n + inst] = out[c];
         }
         if (sample) {
             const double p0 = g.bcast(cellPressure(s.chamber), 0);
             const double pMan = g.bcast(cellPressure(s.plenum), k.plen0Lane);
-            if (g.lane == 0) {
+            if (g.lane == 0 && live) {
                 const long long idx = (gstep + 1) / a.telemetryEvery - 1 - a.telemetryBase;
                 double *t = a.telemetry + (size_t)idx * ESB_TELEMETRY_STRIDE * n + inst;
                 t[0 * n] = -s.crank.w * (30.0 / kPi);
@@ -146,6 +146,7 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, const Group<G> &g) {
     }
 
     // ---- store ----
+    if (!live) return;
     if (g.lane == 0) {
         storeBody(s.crank, S, n, (size_t)ESB_GF_CRANK * n + inst);
         storeBody(s.veh, S, n, (size_t)ESB_GF_VEH * n + inst);

@@ -147,6 +147,10 @@ int32_t EsbBatchGetStats(EsbBatchHandle b, int32_t instance, EngineSimStats *out
 int32_t EsbBatchWriteWavs(EsbBatchHandle b, const char *directory, const char *prefix); /* last render, one mono WAV per instance */
 /* Launch geometry of the physics kernel: threads per block (multiple of 32), steps per launch */
 int32_t EsbBatchSetLaunchConfig(EsbBatchHandle b, int32_t blockThreads, int32_t stepsPerLaunch);
+/* Shape of the physics launch: instances per warp (0 = as many as fit: 32 / lanes-per-instance; fewer leaves
+ * warps part-empty but puts more warps in flight, which is faster when the batch cannot fill the GPU) and the
+ * register budget of the kernel build (0: 255 registers, 1: 146, 2: 128; results are identical). */
+int32_t EsbBatchSetPhysicsShape(EsbBatchHandle b, int32_t instPerWarp, int32_t variant);
 /* Kernel launches issued so far by this batch (physics, synth-pre, fir, synth-post) */
 int32_t EsbBatchGetLaunchCounts(EsbBatchHandle b, int64_t counts[4]);
 

@@ -29,7 +29,7 @@ template <int G> static void runGroup(const esbk::RunArgs &a, int inst) {
     for (int lane = 0; lane < G; ++lane)
         th.emplace_back([&, lane] {
             esbk::Group<G> g; g.lane = lane; g.mask = 0; g.sh = &sh;
-            esbk::runInstance<G>(a, inst, g);
+            esbk::runInstance<G>(a, inst, true, g);
         });
     for (auto &t : th) t.join();
 }
