@@ -1,6 +1,7 @@
 // capi.cpp — C interface of the oracle for ctypes (TEST INFRASTRUCTURE ONLY).
 // Called from tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
 #include "oracle.h"
+#include "esb_math.h"
 
 #include <chrono>
 #include <cstring>
@@ -135,6 +136,12 @@ void orc_fir_f64(const float *x, int channels, int n, const float *h, int L, int
         }
     }
 }
+
+// deterministic math of include/esb_math.h, for tests/test_math.py: 0 sin, 1 cos, 2 log, 3 exp, 4 pow
+double orc_math(int fn, double x, double y) {
+    switch (fn) { case 0: return esb_sin(x); case 1: return esb_cos(x); case 2: return esb_log(x); case 3: return esb_exp(x); default: return esb_pow(x, y); }
+}
+double orc_rand_u01(uint64_t seed, uint64_t stream, uint64_t counter) { return esb_rand_u01(seed, stream, counter); }
 
 double orc_sample_function(const EsbEngineParams *p, int fn, double x) { return sampleTriangle(*p, fn, x); }
 int orc_params_size() { return (int)sizeof(EsbEngineParams); }
