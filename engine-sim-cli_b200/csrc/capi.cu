@@ -209,6 +209,7 @@ int32_t EsbProbePeak(int32_t fp64, int32_t fma, double *outGflops) {
 // ---------------------------------------------------------------------------------------
 // single simulator
 const char *EngineSimGetVersion(void) { return "1.0.0-b200"; }
+const char *EsbGetVersion(void) { return "1.0.0-b200"; }
 
 int32_t EngineSimCreate(const EngineSimConfig *config, EngineSimHandle *out) {
     if (!out) return ESIM_ERROR_INVALID_PARAMETER;

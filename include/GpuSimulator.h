@@ -1,0 +1,89 @@
+// GpuSimulator.h — header-only adapter: the reference's ICombustionEngine / ISimulator interface
+// (engine-sim-bridge/include/simulator/ISimulator.h:12-45, ICombustionEngine.h) implemented over
+// the C ABI of libenginesim_b200.so (engine_sim_b200.h).  It compiles against the reference's own
+// headers only (ISimulator.h, ICombustionEngine.h, EngineSimTypes.h, EnginePhase.h) and is the
+// file a maintainer drops into engine-sim-bridge/include/simulator/ (see INTEGRATION.md); the
+// SimulationLoop / SyncPullStrategy / CrankingController callers then drive it unchanged.
+//
+// Semantics follow BridgeSimulator (engine-sim-bridge/src/simulator/BridgeSimulator.cpp):
+//   renderOnDemand throws on null / non-positive arguments (:67-68), destroy() is idempotent
+//   (:45-51), setThrottle clamps (:183-189), update() = ceil(simFreq*dt) steps (:61-64).
+#pragma once
+#include "simulator/ICombustionEngine.h" // reference header (defines ATG_ENGINE_SIM_BRIDGE_H via EngineSimTypes.h)
+#include "engine_sim_b200.h"
+
+#include <stdexcept>
+#include <string>
+
+class GpuSimulator final : public ICombustionEngine {
+public:
+    ~GpuSimulator() override { destroy(); }
+
+    bool create(const ISimulatorConfig &c, ILogging * /*logger*/, telemetry::ITelemetryWriter * /*telemetry*/) override {
+        destroy();
+        EngineSimConfig k{};
+        k.sampleRate = c.sampleRate; k.simulationFrequency = c.simulationFrequency; k.fluidSimulationSteps = c.fluidSimulationSteps;
+        k.maxChunkFrames = c.maxChunkFrames; k.targetSynthesizerLatency = c.targetSynthesizerLatency;
+        k.volume = c.volume; k.convolutionLevel = c.convolutionLevel; k.airNoise = -1.0f; k.seed = 0;
+        const int32_t rc = EngineSimCreate(&k, &h_);
+        if (rc != ESIM_SUCCESS) { createError_ = EngineSimGetLastError(nullptr); h_ = nullptr; }
+        return rc == ESIM_SUCCESS;
+    }
+    // SimulatorFactory::create passes (scriptPath, assetBasePath) (SimulatorFactory.cpp:134-156)
+    bool loadScript(const std::string &presetPath, const std::string &assetBasePath) {
+        return h_ && EngineSimLoadScript(h_, presetPath.c_str(), assetBasePath.c_str()) == ESIM_SUCCESS;
+    }
+    // same, from memory (flat parameter blob + one mono s16 impulse response for every exhaust system)
+    bool loadParams(const EsbEngineParams *params, const int16_t *ir, int32_t irCount, float irVolume) {
+        return h_ && EngineSimLoadParams(h_, params, ir, irCount, irVolume) == ESIM_SUCCESS;
+    }
+    void destroy() override { if (h_) { EngineSimDestroy(h_); h_ = nullptr; } }
+    std::string getLastError() const override { return h_ ? EngineSimGetLastError(h_) : createError_; }
+    const char *getName() const override { return "GpuSimulator (B200)"; }
+
+    void update(double dt) override { if (h_) EngineSimUpdate(h_, dt); }
+    bool renderOnDemand(float *buffer, int32_t frames, int32_t *written) override {
+        if (!buffer) throw std::runtime_error("GpuSimulator::renderOnDemand() called with null buffer");
+        if (frames <= 0) throw std::runtime_error("GpuSimulator::renderOnDemand() called with invalid frame count");
+        return h_ && EngineSimRender(h_, buffer, frames, written) == ESIM_SUCCESS;
+    }
+    bool readAudioBuffer(float *buffer, int32_t frames, int32_t *read) override {
+        if (read) *read = 0;
+        if (frames <= 0) return false; // BridgeSimulator.cpp:85-98
+        return h_ && EngineSimReadAudioBuffer(h_, buffer, frames, read) == ESIM_SUCCESS;
+    }
+    bool start() override { return h_ != nullptr; }
+    void stop() override {}
+    int getSimulationFrequency() const override { int32_t f = 0; if (h_) EngineSimGetSimulationFrequency(h_, &f); return f; }
+
+    void setThrottle(double x) override { if (h_) EngineSimSetThrottle(h_, x); }
+    void setStarterMotor(bool on) override { if (h_) EngineSimSetStarterMotor(h_, on ? 1 : 0); }
+    void setIgnition(bool on) override { if (h_) EngineSimSetIgnition(h_, on ? 1 : 0); }
+    void applyTransition(const TransitionDecision &d) override { // phase + starter together (ICombustionEngine.h)
+        phase_ = d.targetPhase;
+        setStarterMotor(d.starterMotor);
+    }
+    EnginePhase getEnginePhase() const override { return phase_; }
+    void setClutchPressure(double p) override { if (h_) EngineSimSetClutchPressure(h_, p); }
+    void setBrakePressure(double p) override { if (h_) EngineSimSetBrake(h_, p); }
+    double getEngineRpm() const override { return getStats().currentRPM; }
+    // hold-mode dynamometer as BridgeSimulator::configureDynoLoad wires it (BridgeSimulator.cpp:323-332)
+    void configureDyno(bool enabled, bool hold, double rpm, double maxTorqueNm) { if (h_) EngineSimSetDyno(h_, enabled, hold, rpm, maxTorqueNm); }
+
+    EngineSimStats getStats() const override {
+        EngineSimStats out; // the reference's C++ struct (EngineSimTypes.h:108-133)
+        EsbSimStats s{};
+        if (h_ && EngineSimGetStats(h_, &s) == ESIM_SUCCESS) {
+            out.currentRPM = s.currentRPM; out.currentLoad = s.currentLoad; out.exhaustFlow = s.exhaustFlow;
+            out.manifoldPressure = s.manifoldPressure; out.activeChannels = s.activeChannels; out.processingTimeMs = s.processingTimeMs;
+            out.dynoTorque = s.dynoTorque; out.dynoTargetRPM = s.dynoTargetRPM; out.dynoTorqueScale = s.dynoTorqueScale; out.gear = s.gear;
+            out.vehicleSpeedKmh = s.vehicleSpeedKmh; out.engineTorqueNm = s.engineTorqueNm; out.drivetrainTorqueNm = s.drivetrainTorqueNm;
+        }
+        return out;
+    }
+
+private:
+    EngineSimHandle h_ = nullptr;
+    EnginePhase phase_ = EnginePhase::Stopped;
+    std::string createError_;
+};

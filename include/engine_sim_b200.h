@@ -59,7 +59,10 @@ int32_t EngineSimLoadScript(EngineSimHandle h, const char *scriptPath, const cha
 int32_t EngineSimLoadParams(EngineSimHandle h, const EsbEngineParams *params, const int16_t *irSamples, int32_t irCount, float irVolume);
 int32_t EngineSimDestroy(EngineSimHandle h);                       /* ISimulator::destroy, idempotent (BridgeSimulator.cpp:45-51) */
 const char *EngineSimGetLastError(EngineSimHandle h);              /* ISimulator::getLastError */
-const char *EngineSimGetVersion(void);                             /* EngineSimTypes.h:176-178 */
+#ifndef ATG_ENGINE_SIM_BRIDGE_H /* the reference defines an inline function of this name (EngineSimTypes.h:176-178) */
+const char *EngineSimGetVersion(void);
+#endif
+const char *EsbGetVersion(void);
 
 int32_t EngineSimSetThrottle(EngineSimHandle h, double position);  /* clamps to [0,1] (BridgeSimulator.cpp:183-189) */
 int32_t EngineSimSetSpeedControl(EngineSimHandle h, double position);
@@ -80,7 +83,7 @@ int32_t EngineSimRender(EngineSimHandle h, float *buffer, int32_t frames, int32_
 int32_t EngineSimReadAudioBuffer(EngineSimHandle h, float *buffer, int32_t frames, int32_t *outRead);
 /* mono int16 variant of the same read (Simulator::readAudioOutput) */
 int32_t EngineSimReadAudioInt16(EngineSimHandle h, int16_t *buffer, int32_t frames, int32_t *outRead);
-int32_t EngineSimGetStats(EngineSimHandle h, EngineSimStats *outStats); /* ISimulator::getStats (:114-181) */
+int32_t EngineSimGetStats(EngineSimHandle h, EsbSimStats *outStats); /* ISimulator::getStats (:114-181) */
 int32_t EngineSimGetSimulationFrequency(EngineSimHandle h, int32_t *outHz);
 
 /* ------------------------------------------------------------------------------------- */
@@ -143,7 +146,7 @@ int32_t EsbBatchGetState(EsbBatchHandle b, double *out, int32_t *outFields);
 /* Synthesizer input stream of the last render chunk is not kept; this re-runs nothing: copies the
  * per-step exhaust stream of the LAST physics launch [steps][channels][nInstances]. */
 int32_t EsbBatchGetLastStream(EsbBatchHandle b, double *out, int32_t maxSteps, int32_t *outSteps);
-int32_t EsbBatchGetStats(EsbBatchHandle b, int32_t instance, EngineSimStats *out);
+int32_t EsbBatchGetStats(EsbBatchHandle b, int32_t instance, EsbSimStats *out);
 int32_t EsbBatchWriteWavs(EsbBatchHandle b, const char *directory, const char *prefix); /* last render, one mono WAV per instance */
 /* Launch geometry of the physics kernel: threads per block (multiple of 32), steps per launch */
 int32_t EsbBatchSetLaunchConfig(EsbBatchHandle b, int32_t blockThreads, int32_t stepsPerLaunch);

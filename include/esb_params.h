@@ -127,7 +127,7 @@ typedef struct EngineSimConfig {
 
 /* Telemetry snapshot; field-for-field the reference's EngineSimStats
  * (EngineSimTypes.h:108-133) flattened to C. */
-typedef struct EngineSimStats {
+typedef struct EsbSimStats {
     double currentRPM;
     double currentLoad;
     double exhaustFlow;
@@ -143,7 +143,13 @@ typedef struct EngineSimStats {
     double drivetrainTorqueNm;
     int32_t gearSelector;
     int32_t gearAutoMode;
-} EngineSimStats;
+} EsbSimStats;
+/* The reference's own EngineSimTypes.h (include guard ATG_ENGINE_SIM_BRIDGE_H) defines a C++ struct of this
+ * name with a different member order; when both headers meet in one translation unit (include/GpuSimulator.h)
+ * only the Esb name exists and the adapter converts field by field. */
+#ifndef ATG_ENGINE_SIM_BRIDGE_H
+typedef EsbSimStats EngineSimStats;
+#endif
 
 #ifdef __cplusplus
 }
