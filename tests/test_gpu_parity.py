@@ -228,22 +228,21 @@ def test_errors_and_edge_cases(gm_ls_blob):
     assert pcm.shape[1] in (4, 5)
 
 
-def test_offline_renderer_cli(tmp_path, gm_ls_blob, gm_ls_ir):
+def test_offline_renderer_cli(tmp_path):
     """The batch WAV renderer (reference CLI flag names + the README's --rpm): files exist, have the
-    RealEngineAudioSpike header layout (mono) and the expected length; RMS > 0.01 (RealEngineAudioSpike.cpp:267-268)."""
-    import json
+    RealEngineAudioSpike header layout (mono) and the expected length, RMS > 0.01 (RealEngineAudioSpike.cpp:267-268),
+    telemetry CSV has one row per 100 steps per instance."""
     import wave
+    from conftest import GOLDEN
     from engine_sim_cli_b200 import render
-    # a preset JSON is needed: rebuild one is not possible on the GPU box, so drive the same code through a tiny shim preset
-    # made from the committed blob via the API instead of --script when the reference fixtures are absent
-    fixture = "/root/reference/engine-sim-bridge/test/fixtures/gm_ls.preset.json"
-    if not os.path.exists(fixture):
-        pytest.skip("preset JSON fixture lives in the reference checkout")
-    rc = render.main(["--script", fixture, "--assets", "/root/reference/engine-sim-bridge/es", "--rpm", "1500:3000:3", "--duration", "0.6",
-                      "--output", str(tmp_path / "out"), "--telemetry", str(tmp_path / "tel.csv")])
+    rc = render.main(["--script", os.path.join(GOLDEN, "gm_ls.params.bin"), "--ir", os.path.join(GOLDEN, "gm_ls.ir.npy"), "--rpm", "1500:3000:3",
+                      "--duration", "1.0", "--output", str(tmp_path / "out"), "--telemetry", str(tmp_path / "tel.csv")])
     assert rc == 0
     for i in range(3):
         w = wave.open(str(tmp_path / "out" / f"engine_{i:05d}.wav"))
         assert w.getnchannels() == 1 and w.getsampwidth() == 2 and w.getframerate() == 44100
-        assert abs(w.getnframes() - 0.6 * 44100) <= 5
-    assert len(open(tmp_path / "tel.csv").read().splitlines()) == 1 + 3 * 60
+        assert abs(w.getnframes() - 44100) <= 5
+        s16 = np.frombuffer(w.readframes(w.getnframes()), dtype=np.int16).astype(np.float64) / 32768.0
+        assert math.sqrt((s16[len(s16) // 2:] ** 2).mean()) > 0.01
+    assert len(open(tmp_path / "tel.csv").read().splitlines()) == 1 + 3 * 100
+    assert render.main(["--script", "engine.mr", "--output", str(tmp_path / "x")]) == 2
