@@ -88,9 +88,25 @@ ESB_HD void esb_sincos(double x, double *s_out, double *c_out) {
 ESB_HD double esb_sin(double x) { double s, c; esb_sincos(x, &s, &c); return s; }
 ESB_HD double esb_cos(double x) { double s, c; esb_sincos(x, &s, &c); return c; }
 
-/* ---- log --------------------------------------------------------------- */
+/* ---- log / exp / pow ------------------------------------------------------ */
+/* Each contains one division.  The bodies are written once, over a divider `dv`, so the CUDA
+ * physics kernel can supply its straight-line correctly-rounded division (physics_core.cuh
+ * FastAr) while the oracle and everything else use the plain IEEE `/`: same value either way. */
+#ifdef __cplusplus
+struct EsbIeeeDiv {
+    ESB_HD double div(double a, double b) { return a / b; }
+};
+#define ESB_DIV_TEMPLATE template <class DV>
+#define ESB_DIV_ARG , DV &dv
+#define ESB_DIV(a, b) dv.div((a), (b))
+#else
+#define ESB_DIV_TEMPLATE
+#define ESB_DIV_ARG
+#define ESB_DIV(a, b) ((a) / (b))
+#endif
+
 /* x > 0, finite, normal. */
-ESB_HD double esb_log(double x) {
+ESB_DIV_TEMPLATE ESB_HD double esb_log_t(double x ESB_DIV_ARG) {
     const double LN2_HI = 6.93147180369123816490e-01;
     const double LN2_LO = 1.90821492927058770002e-10;
     int64_t b = esb_d2bits(x);
@@ -101,7 +117,7 @@ ESB_HD double esb_log(double x) {
     else { mant |= 0x3ff0000000000000LL; }
     double m = esb_bits2d(mant);
     double f = m - 1.0;
-    double s = f / (2.0 + f);
+    double s = ESB_DIV(f, 2.0 + f);
     double z = s * s;
     double w = z * z;
     double t1 = w * esb_fma(w, esb_fma(w, 1.531383769920937332e-01, 2.222219843214978396e-01), 3.999999999940941908e-01);
@@ -112,11 +128,11 @@ ESB_HD double esb_log(double x) {
     return dk * LN2_HI - ((hfsq - (s * (hfsq + R) + dk * LN2_LO)) - f);
 }
 
-/* ---- exp --------------------------------------------------------------- */
 /* Flushes to 0 below -700 and saturates above 700 (no subnormal results). */
-ESB_HD double esb_exp(double x) {
-    if (x < -700.0) return 0.0;
+ESB_DIV_TEMPLATE ESB_HD double esb_exp_t(double x ESB_DIV_ARG) {
+    const bool under = x < -700.0;
     if (x > 700.0) x = 700.0;
+    if (under) x = -700.0;
     const double LN2_HI = 6.93147180369123816490e-01;
     const double LN2_LO = 1.90821492927058770002e-10;
     const double INV_LN2 = 1.44269504088896338700e+00;
@@ -126,17 +142,34 @@ ESB_HD double esb_exp(double x) {
     double r = hi - lo;
     double t = r * r;
     double c = r - t * esb_fma(t, esb_fma(t, esb_fma(t, esb_fma(t, 4.13813679705723846039e-08, -1.65339022054652515390e-06), 6.61375632143793436117e-05), -2.77777777770155933842e-03), 1.66666666666666019037e-01);
-    double y = 1.0 - ((lo - (r * c) / (2.0 - c)) - hi);
+    double y = 1.0 - ((lo - ESB_DIV(r * c, 2.0 - c)) - hi);
     int64_t k = (int64_t)kf;
     /* scale by 2^k (k within the normal range for our arguments) */
-    return y * esb_bits2d((k + 1023) << 52);
+    y = y * esb_bits2d((k + 1023) << 52);
+    return under ? 0.0 : y;
 }
 
 /* pow for x >= 0 (the only case the gas model needs). */
-ESB_HD double esb_pow(double x, double y) {
-    if (x <= 0.0) return (y == 0.0) ? 1.0 : 0.0;
-    return esb_exp(y * esb_log(x));
+ESB_DIV_TEMPLATE ESB_HD double esb_pow_t(double x, double y ESB_DIV_ARG) {
+    const bool nonpos = x <= 0.0;
+    const double xs = nonpos ? 1.0 : x;
+#ifdef __cplusplus
+    const double r = esb_exp_t(y * esb_log_t(xs, dv), dv);
+#else
+    const double r = esb_exp_t(y * esb_log_t(xs));
+#endif
+    return nonpos ? ((y == 0.0) ? 1.0 : 0.0) : r;
 }
+
+#ifdef __cplusplus
+ESB_HD double esb_log(double x) { EsbIeeeDiv d; return esb_log_t(x, d); }
+ESB_HD double esb_exp(double x) { EsbIeeeDiv d; return esb_exp_t(x, d); }
+ESB_HD double esb_pow(double x, double y) { EsbIeeeDiv d; return esb_pow_t(x, y, d); }
+#else
+ESB_HD double esb_log(double x) { return esb_log_t(x); }
+ESB_HD double esb_exp(double x) { return esb_exp_t(x); }
+ESB_HD double esb_pow(double x, double y) { return esb_pow_t(x, y); }
+#endif
 
 /* ---- counter-based noise ---------------------------------------------- */
 /* Replaces libc rand() (platform-specific stream).  A splitmix64-style mix of
