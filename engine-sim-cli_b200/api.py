@@ -65,6 +65,7 @@ def lib():
             "EsbBatchSetLaunchConfig": [vp, i32, i32], "EsbBatchGetLaunchCounts": [vp, vp],
             "EsbBatchSetProfiling": [vp, i32], "EsbBatchSetPhysicsShape": [vp, i32, i32], "EsbBatchGetKernelTimes": [vp, vp, vp],
             "EsbFirRun": [vp, i64, i64, vp, i32, i32, i32, i32, i64, vp, i64, vp], "EsbProbePeak": [i32, i32, C.POINTER(dbl)],
+            "EsbCheckFastArith": [i32, i32, vp, vp, vp, vp],
             "EngineSimCreate": [vp, C.POINTER(vp)], "EngineSimLoadScript": [vp, C.c_char_p, C.c_char_p], "EngineSimLoadParams": [vp, vp, vp, i32, flt],
             "EngineSimDestroy": [vp], "EngineSimSetThrottle": [vp, dbl], "EngineSimSetSpeedControl": [vp, dbl], "EngineSimSetIgnition": [vp, i32],
             "EngineSimSetStarterMotor": [vp, i32], "EngineSimSetDyno": [vp, i32, i32, dbl, dbl], "EngineSimSetClutchPressure": [vp, dbl],
@@ -357,3 +358,15 @@ def probe_peak(fp64, fma):
     if rc != ESIM_SUCCESS:
         raise EngineSimError(rc, "EsbProbePeak failed")
     return out.value
+
+
+def check_fast_arith(op, a, b=None):
+    """The physics kernel's branch-free division (op 0) / sqrt (op 1) on host arrays: (result, flagged)."""
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    b = np.ascontiguousarray(b, dtype=np.float64) if b is not None else None
+    out = np.zeros_like(a)
+    flagged = np.zeros(a.shape, dtype=np.uint32)
+    rc = lib().EsbCheckFastArith(op, a.size, _ptr(a), _ptr(b), _ptr(out), _ptr(flagged))
+    if rc != 0:
+        raise EngineSimError(rc, "EsbCheckFastArith failed")
+    return out, flagged

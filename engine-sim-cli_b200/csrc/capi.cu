@@ -180,6 +180,22 @@ int32_t EsbFirRun(const float *dX, int64_t xStride, int64_t hist, const float *d
     return ESIM_SUCCESS;
 }
 
+int32_t EsbCheckFastArith(int32_t op, int32_t n, const double *a, const double *b, double *out, uint32_t *flagged) {
+    if (n <= 0 || !a || !out || !flagged || (op == 0 && !b) || (op != 0 && op != 1)) return ESIM_ERROR_INVALID_PARAMETER;
+    double *dA = nullptr, *dB = nullptr, *dO = nullptr;
+    unsigned *dF = nullptr;
+    const size_t bytes = (size_t)n * sizeof(double);
+    bool ok = cudaMalloc(&dA, bytes) == cudaSuccess && cudaMalloc(&dB, bytes) == cudaSuccess && cudaMalloc(&dO, bytes) == cudaSuccess &&
+              cudaMalloc(&dF, (size_t)n * sizeof(unsigned)) == cudaSuccess;
+    ok = ok && cudaMemcpy(dA, a, bytes, cudaMemcpyHostToDevice) == cudaSuccess;
+    ok = ok && cudaMemcpy(dB, b ? b : a, bytes, cudaMemcpyHostToDevice) == cudaSuccess;
+    ok = ok && esbLaunchFastArCheck(op, n, dA, dB, dO, dF, 0) == cudaSuccess;
+    ok = ok && cudaMemcpy(out, dO, bytes, cudaMemcpyDeviceToHost) == cudaSuccess;
+    ok = ok && cudaMemcpy(flagged, dF, (size_t)n * sizeof(unsigned), cudaMemcpyDeviceToHost) == cudaSuccess;
+    cudaFree(dA); cudaFree(dB); cudaFree(dO); cudaFree(dF);
+    return ok ? ESIM_SUCCESS : ESIM_ERROR_CUDA;
+}
+
 int32_t EsbProbePeak(int32_t fp64, int32_t fma, double *outGflops) {
     if (!outGflops) return ESIM_ERROR_INVALID_PARAMETER;
     int dev = 0, sms = 0;

@@ -84,3 +84,6 @@ cudaError_t esbLaunchSine(double *stream, int nSteps, int channels, int nInst, c
 
 // FP32 / FP64 pipe peak probes (peak_probe.cu): register-resident FMA loops, returns ops issued
 cudaError_t esbLaunchPeakProbe(int fp64, int fma, int blocks, int threads, int iters, float *sink, cudaStream_t stream);
+
+// Self-check of the physics kernel's straight-line division / sqrt (physics_kernel.cu; device pointers)
+cudaError_t esbLaunchFastArCheck(int op, int n, const double *a, const double *b, double *out, unsigned *flagged, cudaStream_t stream);

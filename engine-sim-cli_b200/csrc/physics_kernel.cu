@@ -32,6 +32,20 @@ __global__ void __launch_bounds__(256, (MINB >= 7 ? 2 : 1)) esb_physics_kernel(R
 
 } // namespace esbk
 
+// Self-check of the kernel's straight-line arithmetic (FastAr): out[i] = a[i] / b[i] (op 0) or sqrt(a[i]) (op 1),
+// flagged[i] = 1 where FastAr would hand the exchange to the exact path instead.
+__global__ void esb_fastar_check_kernel(int op, int n, const double *a, const double *b, double *out, unsigned *flagged) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    esbk::FastAr ar;
+    out[i] = (op == 0) ? ar.div(a[i], b[i]) : ar.sqrt(a[i]);
+    flagged[i] = ar.bad;
+}
+cudaError_t esbLaunchFastArCheck(int op, int n, const double *a, const double *b, double *out, unsigned *flagged, cudaStream_t stream) {
+    esb_fastar_check_kernel<<<(n + 255) / 256, 256, 0, stream>>>(op, n, a, b, out, flagged);
+    return cudaGetLastError();
+}
+
 template <int G>
 static cudaError_t launchG(const esbk::RunArgs &a, int blockThreads, int instPerWarp, int variant, cudaStream_t stream) {
     const int full = 32 / G;

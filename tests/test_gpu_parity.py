@@ -246,3 +246,46 @@ def test_offline_renderer_cli(tmp_path):
         assert math.sqrt((s16[len(s16) // 2:] ** 2).mean()) > 0.01
     assert len(open(tmp_path / "tel.csv").read().splitlines()) == 1 + 3 * 100
     assert render.main(["--script", "engine.mr", "--output", str(tmp_path / "x")]) == 2
+
+
+def test_fast_arithmetic_is_ieee():
+    """The physics kernel's branch-free division / sqrt (FastAr, physics_core.cuh) must equal the IEEE-754
+    correctly rounded operation bit for bit wherever it does not flag the operands for the exact path, and
+    must flag (never mis-compute) everything outside its range."""
+    esb = _esb()
+    rng = np.random.default_rng(42)
+    n = 1 << 21
+    # magnitudes the gas model sees (1e-12 .. 1e12), both signs, plus exact ties / powers of two / zeros
+    a = rng.standard_normal(n) * 10.0 ** rng.uniform(-12, 12, n)
+    b = rng.standard_normal(n) * 10.0 ** rng.uniform(-12, 12, n)
+    a[:1000] = 0.0
+    a[1000:2000] = -0.0
+    b[:500] = np.abs(b[:500]); b[500:1000] = -np.abs(b[500:1000])
+    a[2000:3000] = np.ldexp(1.0, rng.integers(-40, 40, 1000)); b[2000:3000] = np.ldexp(1.0, rng.integers(-40, 40, 1000))
+    a[3000:4000] = rng.integers(1, 1 << 20, 1000).astype(np.float64); b[3000:4000] = rng.integers(1, 1 << 20, 1000).astype(np.float64)
+    # near-tie quotients: a = q * b with q, b short mantissas
+    qs = rng.integers(1 << 25, 1 << 26, 1000).astype(np.float64); bs = rng.integers(1 << 25, 1 << 26, 1000).astype(np.float64)
+    a[4000:5000] = qs * bs + rng.integers(-1, 2, 1000); b[4000:5000] = bs
+    out, flagged = esb.check_fast_arith(0, a, b)
+    with np.errstate(all="ignore"):
+        want = a / b
+    live = flagged == 0
+    assert live.mean() > 0.999
+    assert np.array_equal(out[live].view(np.uint64), want[live].view(np.uint64))
+    assert live[:2000].all()  # signed zero numerators stay on the fast path, with the right sign (checked bitwise above)
+    # operands outside the exact range must be flagged, whatever they compute to
+    wa = np.array([1.0, 0.0, np.inf, np.nan, 1.0, 1e-300, 1e300, 5e-324, 1.0, 1.0, -0.0, 1e-310])
+    wb = np.array([0.0, 0.0, 1.0, 1.0, np.inf, 1e300, 1e-300, 1.0, np.nan, 5e-324, 0.0, 3.0])
+    _, f = esb.check_fast_arith(0, wa, wb)
+    assert (f == 1).all()
+    # square root
+    x = np.abs(a)
+    x[5000:6000] = rng.integers(1, 1 << 26, 1000).astype(np.float64) ** 2  # exact squares
+    out, flagged = esb.check_fast_arith(1, x)
+    live = flagged == 0
+    assert live.mean() > 0.999
+    assert np.array_equal(out[live].view(np.uint64), np.sqrt(x[live]).view(np.uint64))
+    _, f = esb.check_fast_arith(1, np.array([-1.0, np.inf, np.nan, 5e-324, 1e-310]))
+    assert (f == 1).all()
+    out, f = esb.check_fast_arith(1, np.array([0.0, -0.0]))
+    assert (f == 0).all() and np.array_equal(out.view(np.uint64), np.array([0.0, -0.0]).view(np.uint64))
