@@ -39,7 +39,7 @@ __global__ void esb_fastar_check_kernel(int op, int n, const double *a, const do
     if (i >= n) return;
     esbk::FastAr ar;
     out[i] = (op == 0) ? ar.div(a[i], b[i]) : ar.sqrt(a[i]);
-    flagged[i] = ar.bad;
+    flagged[i] = ar.failed() ? 1u : 0u;
 }
 cudaError_t esbLaunchFastArCheck(int op, int n, const double *a, const double *b, double *out, unsigned *flagged, cudaStream_t stream) {
     esb_fastar_check_kernel<<<(n + 255) / 256, 256, 0, stream>>>(op, n, a, b, out, flagged);
