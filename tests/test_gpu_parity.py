@@ -315,3 +315,16 @@ def test_fast_arithmetic_is_ieee():
     assert (f == 1).all()
     out, f = esb.check_fast_arith(1, np.array([0.0, -0.0]))
     assert (f == 0).all() and np.array_equal(out.view(np.uint64), np.array([0.0, -0.0]).view(np.uint64))
+
+
+def test_fir_microbench_script(tmp_path):
+    """bench_fir.py (BASELINE config 5, reduced): runs through the C ABI, SNR >= 90 dB against FP64 both ways."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench_fir.py"), "--channels", "256", "--taps", "5000", "--samples", "30000",
+                          "--irs", "2", "--chunk", "8000", "--check-samples", "20000"], capture_output=True, text=True, check=True).stdout
+    line = json.loads(out.strip().splitlines()[-1])
+    assert line["snr_db_vs_fp64_fft_64ch"] >= 90.0 and line["snr_db_vs_oracle_direct_fp64"] >= 90.0
+    assert line["value"] > 1.0
