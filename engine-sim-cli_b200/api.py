@@ -143,6 +143,25 @@ class BatchSimulator:
     def load_preset_json(self, text):
         self._check(lib().EsbBatchLoadPresetJson(self.h, text.encode()))
 
+    def load_script(self, path, asset_base=None):
+        """Loads an engine from a preset JSON or an engine-sim `.mr` script (compiled by mr_frontend.py; the impulse
+        responses the script names are read from `asset_base`/sound-library, by default the script library's root)."""
+        if not path.endswith(".mr"):
+            return self.load_preset_file(path, asset_base)
+        import json
+        import tempfile
+
+        from . import mr_frontend
+        doc = mr_frontend.compile_script(path)
+        if asset_base is None:
+            asset_base = mr_frontend.library_root(path)
+        with tempfile.NamedTemporaryFile("w", suffix=".preset.json", delete=False) as f:
+            json.dump(doc, f)
+        try:
+            self.load_preset_file(f.name, asset_base)
+        finally:
+            os.unlink(f.name)
+
     def set_impulse_response(self, exhaust, samples_s16, volume, max_taps=0):
         s = np.ascontiguousarray(samples_s16, dtype=np.int16)
         self._check(lib().EsbBatchSetImpulseResponse(self.h, exhaust, _ptr(s), len(s), float(volume), int(max_taps)))
@@ -293,7 +312,23 @@ class Simulator:
         return msg.decode() if msg else ""
 
     def load_script(self, path, asset_base=None):
-        self._check(lib().EngineSimLoadScript(self.h, path.encode(), asset_base.encode() if asset_base else None))
+        """EngineSimLoadScript: a preset JSON directly; an engine-sim `.mr` script is compiled first (mr_frontend.py)."""
+        tmp = None
+        if path.endswith(".mr"):
+            import json
+            import tempfile
+
+            from . import mr_frontend
+            doc = mr_frontend.compile_script(path)
+            asset_base = asset_base or mr_frontend.library_root(path)
+            with tempfile.NamedTemporaryFile("w", suffix=".preset.json", delete=False) as f:
+                json.dump(doc, f)
+            path = tmp = f.name
+        try:
+            self._check(lib().EngineSimLoadScript(self.h, path.encode(), asset_base.encode() if asset_base else None))
+        finally:
+            if tmp:
+                os.unlink(tmp)
 
     def load_params(self, blob, ir=None, ir_volume=0.001):
         buf = C.create_string_buffer(blob, len(blob))

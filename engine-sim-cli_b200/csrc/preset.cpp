@@ -203,6 +203,12 @@ void parsePreset(const std::string &text, LoadedPreset &out) {
             // CylinderHeadDeserializer.cpp:86-99: bank i -> intake/exhaust i when it exists, else 0
             d.intake = (p.intakeCount > (int)bi) ? (int)bi : 0;
             d.exhaustSystem = (p.exhaustSystemCount > (int)bi) ? (int)bi : 0;
+            // Documents written by the .mr front-end (mr_frontend.py) carry the script's own plumbing per cylinder
+            // (add_cylinder(exhaust_system: ..., intake: ...), es/actions/actions.mr): e.g. an inline four with two collectors.
+            if (c.has("exhaustSystemIndex")) d.exhaustSystem = (int)c.number("exhaustSystemIndex", cc);
+            if (c.has("intakeIndex")) d.intake = (int)c.number("intakeIndex", cc);
+            if (d.exhaustSystem < 0 || d.exhaustSystem >= p.exhaustSystemCount) throw JsonError("exhaustSystemIndex out of range in " + cc);
+            if (d.intake < 0 || d.intake >= p.intakeCount) throw JsonError("intakeIndex out of range in " + cc);
         }
     }
     if (g != p.cylinderCount) throw JsonError("cylinderCount does not match the cylinders listed in cylinderBanks");

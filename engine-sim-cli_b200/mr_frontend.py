@@ -827,16 +827,23 @@ def to_preset(interp, source_script=""):
     return doc
 
 
+def library_root(script_path):
+    """The directory above the script that holds engine_sim.mr (and sound-library/), or None."""
+    d = os.path.dirname(os.path.abspath(script_path))
+    while d and d != os.path.dirname(d):
+        if os.path.isfile(os.path.join(d, "engine_sim.mr")):
+            return d
+        d = os.path.dirname(d)
+    return None
+
+
 def compile_script(script_path, search_paths=None):
     """Evaluates an engine script and returns the preset document (a dict ready for json.dump)."""
     script_path = os.path.abspath(script_path)
     paths = list(search_paths or [])
-    d = os.path.dirname(script_path)
-    while d and d != os.path.dirname(d):       # the library root is the directory that holds engine_sim.mr
-        if os.path.isfile(os.path.join(d, "engine_sim.mr")):
-            paths.append(d)
-            break
-        d = os.path.dirname(d)
+    root = library_root(script_path)
+    if root:
+        paths.append(root)
     interp = Interpreter(paths).run(script_path)
     return to_preset(interp, os.path.basename(script_path))
 

@@ -32,6 +32,15 @@ PRESETS = {
 # The "long IR" of BASELINE config 3 (ferrari_f136: 08_ferrari_f136_v8.mr:248, new/mild_exhaust_reverb.wav,
 # 42,415 frames) is the same file the Honda preset names, so honda_trx520.ir.npy doubles as that fixture.
 EXTRA_IRS = {}
+# Engines that exist only as .mr scripts (BASELINE configs 3-4): compiled by OUR front-end (engine_sim_cli_b200/mr_frontend.py,
+# itself pinned by the three script/preset pairs above), then through the same loader.  Their IRs are stored once per
+# wav file as ir_<name>.npy; mr_manifest.json maps engine -> IR file and volume.
+SCRIPTS = {
+    "ferrari_f136": "es/engines/atg-video-2/08_ferrari_f136_v8.mr",
+    "lfa_v10": "es/engines/atg-video-2/10_lfa_v10.mr",
+    "merlin_v12": "es/engines/atg-video-2/11_merlin_v12.mr",
+    "hayabusa_i4": "es/engines/atg-video-1/04_hayabusa.mr",
+}
 
 
 def read_wav_mono16(path):
@@ -58,6 +67,28 @@ def main():
         ir = read_wav_mono16(os.path.join(REF, "es", irs[0]))
         np.save(os.path.join(HERE, name + ".ir.npy"), ir)
         print(name, r.stdout.splitlines()[0], "ir", irs[0], len(ir))
+    import importlib.util
+    import json
+    spec = importlib.util.spec_from_file_location("mr_frontend", os.path.join(ROOT, "engine-sim-cli_b200", "mr_frontend.py"))
+    mr = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mr)
+    manifest = {}
+    for name, rel in SCRIPTS.items():
+        doc = mr.compile_script(os.path.join(REF, rel))
+        tmp = os.path.join(build, name + ".preset.json")
+        json.dump(doc, open(tmp, "w"))
+        out = os.path.join(HERE, name + ".params.bin")
+        r = subprocess.run([exe, tmp, out], check=True, capture_output=True, text=True)
+        irs = [l.split(" ", 1)[1] for l in r.stdout.splitlines() if l.startswith("ir ")]
+        entry = []
+        for k, irf in enumerate(irs):
+            key = "ir_" + os.path.splitext(os.path.basename(irf))[0] + ".npy"
+            if not os.path.exists(os.path.join(HERE, key)):
+                np.save(os.path.join(HERE, key), read_wav_mono16(os.path.join(REF, "es", irf)))
+            entry.append({"file": key, "volume": doc["engine"]["exhaustSystems"][k]["impulseResponseVolume"]})
+        manifest[name] = {"script": rel, "cylinders": doc["engine"]["cylinderCount"], "irs": entry}
+        print(name, r.stdout.splitlines()[0], [e["file"] for e in entry])
+    json.dump(manifest, open(os.path.join(HERE, "mr_manifest.json"), "w"), indent=1)
     for name, rel in EXTRA_IRS.items():
         ir = read_wav_mono16(os.path.join(REF, rel))
         np.save(os.path.join(HERE, name + ".ir.npy"), ir)
