@@ -152,7 +152,10 @@ class BatchSimulator:
         import tempfile
 
         from . import mr_frontend
-        doc = mr_frontend.compile_script(path)
+        try:
+            doc = mr_frontend.compile_script(path)
+        except mr_frontend.MrError as e:
+            raise EngineSimError(-6, f"script compilation failed: {e}") from e       # ESIM_ERROR_SCRIPT_COMPILATION
         if asset_base is None:
             asset_base = mr_frontend.library_root(path)
         with tempfile.NamedTemporaryFile("w", suffix=".preset.json", delete=False) as f:
@@ -319,7 +322,10 @@ class Simulator:
             import tempfile
 
             from . import mr_frontend
-            doc = mr_frontend.compile_script(path)
+            try:
+                doc = mr_frontend.compile_script(path)
+            except mr_frontend.MrError as e:
+                raise EngineSimError(-6, f"script compilation failed: {e}") from e   # ESIM_ERROR_SCRIPT_COMPILATION
             asset_base = asset_base or mr_frontend.library_root(path)
             with tempfile.NamedTemporaryFile("w", suffix=".preset.json", delete=False) as f:
                 json.dump(doc, f)

@@ -246,7 +246,7 @@ int32_t EngineSimLoadScript(EngineSimHandle h, const char *scriptPath, const cha
     if (!scriptPath) { h->b.lastError = "scriptPath is null"; return ESIM_ERROR_INVALID_PARAMETER; }
     const std::string p(scriptPath);
     if (p.size() >= 3 && p.compare(p.size() - 3, 3, ".mr") == 0) {
-        h->b.lastError = "'.mr' scripts need the Piranha compiler (not part of this library); export a preset JSON with the reference's preset_compiler";
+        h->b.lastError = "'.mr' scripts are compiled by the host-side front-end (engine_sim_cli_b200/mr_frontend.py -> preset JSON; the Python API's load_script does it); pass the resulting preset JSON here";
         return ESIM_ERROR_SCRIPT_COMPILATION;
     }
     h->computed.clear(); h->released = 0;

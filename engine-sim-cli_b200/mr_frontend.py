@@ -840,6 +840,8 @@ def library_root(script_path):
 def compile_script(script_path, search_paths=None):
     """Evaluates an engine script and returns the preset document (a dict ready for json.dump)."""
     script_path = os.path.abspath(script_path)
+    if not os.path.isfile(script_path):
+        raise MrError(f"{script_path}: no such script")
     paths = list(search_paths or [])
     root = library_root(script_path)
     if root:

@@ -51,8 +51,9 @@ typedef struct EngineSimOpaque *EngineSimHandle;
 int32_t EngineSimCreate(const EngineSimConfig *config, EngineSimHandle *outHandle);
 /* SimulatorFactory::create(type, scriptPath, assetBasePath, ...) (SimulatorFactory.cpp:134-156):
  * a *.json preset is loaded directly (loadPresetSimulation, :95-109); impulse responses named by the
- * preset are read relative to assetBasePath (ScriptLoadHelpers.cpp:30-82).  *.mr scripts need the
- * Piranha compiler, which this library does not contain: ESIM_ERROR_SCRIPT_COMPILATION. */
+ * preset are read relative to assetBasePath (ScriptLoadHelpers.cpp:30-82).  *.mr scripts are compiled
+ * to that preset document by the host-side front-end (engine_sim_cli_b200/mr_frontend.py, which the Python
+ * API's load_script and the render CLI call); passed here directly they give ESIM_ERROR_SCRIPT_COMPILATION. */
 int32_t EngineSimLoadScript(EngineSimHandle h, const char *scriptPath, const char *assetBasePath);
 /* Same, from memory: flat parameter blob (sizeof(EsbEngineParams)) and one mono s16 impulse response
  * used for every exhaust system. irSamples may be NULL (identity response). */
