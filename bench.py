@@ -48,9 +48,23 @@ def parse_args():
     ap.add_argument("--variant", type=int, default=0, help="physics kernel register budget: 0 = 255, 1/2 = 128")
     ap.add_argument("--cpu-sim-seconds", type=float, default=1.0, help="engine time per core of the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--engine", default="gm_ls", help="engine of the ensemble: gm_ls (the metric's V8) | subaru_ej25 | honda_trx520 | ferrari_f136 | "
+                    "lfa_v10 | merlin_v12 | hayabusa_i4 (tests/golden/*.params.bin; the last four are compiled from the reference's .mr scripts). "
+                    "A comma list gives rank r the engine names[r % len]: BASELINE config 4's mixed sweep, one engine type per GPU")
     ap.add_argument("--ir-taps", type=int, default=0, help="0 = the preset's exhaust IR (smooth_39.wav, 6907 taps after the reference's clip); N = a "
                     "synthetic N-tap IR (decaying noise, every tap above the clip threshold): BASELINE config 3's long-IR variant, e.g. 33705")
     return ap.parse_args()
+
+
+def load_engine(name):
+    """(parameter blob, [(ir int16, volume) per exhaust system]) of one golden engine."""
+    blob = open(os.path.join(GOLDEN, name + ".params.bin"), "rb").read()
+    n_ex = int(np.frombuffer(blob[:16], dtype=np.int32)[2])
+    man = json.load(open(os.path.join(GOLDEN, "mr_manifest.json")))
+    if name in man:
+        return blob, [(np.load(os.path.join(GOLDEN, e["file"])), e["volume"]) for e in man[name]["irs"]]
+    vol = {"gm_ls": 0.001}.get(name, 0.01)   # impulse_responses.mr: smooth_39 0.001, the new/ files 0.01
+    return blob, [(np.load(os.path.join(GOLDEN, name + ".ir.npy")), vol)] * n_ex
 
 
 def load_workload(ir_taps=0):
@@ -74,6 +88,9 @@ def instance_grid(n, offset=0):
 # ---------------------------------------------------------------------------------------------
 # CPU arm: the oracle, one instance per host thread (ctypes releases the GIL)
 def workload_name(args):
+    if args.engine != "gm_ls":
+        return (f"{args.instances} instances per GPU of [{args.engine}] (one engine type per rank, RPM 64 x throttle 64 grid), sim-freq 10 kHz, "
+                "44.1 kHz, each engine's own exhaust IR as the reference clips it")
     ir = "IR smooth_39 (6907 taps)" if args.ir_taps <= 0 else f"synthetic long IR ({args.ir_taps} taps)"
     return f"{args.instances}-instance v8_gm_ls ensemble (RPM 64 x throttle 64 grid), sim-freq 10 kHz, 44.1 kHz, {ir}"
 
@@ -196,8 +213,15 @@ def b200_main(args, rank, world, local_rank):
     torch.cuda.set_stream(side)
     stream = side.cuda_stream
     b = esb.BatchSimulator(n, device=local_rank, sim_freq=SIM_FREQ, seed=rank * n, stream=stream)
-    b.load_params(blob)
-    taps = [b.set_impulse_response(c, ir, 0.001, max(args.ir_taps, 0)) for c in range(2)]
+    if args.engine != "gm_ls":
+        names = args.engine.split(",")
+        blob, irs = load_engine(names[rank % len(names)])
+        b.load_params(blob)
+        taps = [b.set_impulse_response(c, x, v) for c, (x, v) in enumerate(irs)]
+        ir = irs[0][0]
+    else:
+        b.load_params(blob)
+        taps = [b.set_impulse_response(c, ir, 0.001, max(args.ir_taps, 0)) for c in range(2)]
     b.set_launch_config(args.block_threads, args.steps_per_launch)
     b.set_physics_shape(args.inst_per_warp, args.variant)
     rpm, thr = instance_grid(n, rank * n)
@@ -294,11 +318,11 @@ def main():
     fp64_fma = esb.probe_peak(1, 1) * 1e-3   # TFLOP/s, FMA = 2 flops
     fp64_sep = esb.probe_peak(1, 0) * 1e-3   # separate mul + add (how the physics must issue: no contraction)
     fp32_fma = esb.probe_peak(0, 1) * 1e-3
-    ops = flops.get("fp64_ops_per_instance_step_v8")
+    ops = flops.get("fp64_ops_per_instance_step_v8") if args.engine == "gm_ls" else None   # counted on the oracle for the V8 only
     # launches of one render alternate between full and remainder chunks; use the totals
     total_inst_steps = n * steps * args.steps
     achieved = (ops * total_inst_steps / (phys_ms * 1e-3) * 1e-12) if ops else None
-    roofline = {"bound": "fp64", "kernel": "esb_physics_kernel<8>", "achieved": achieved, "peak": fp64_fma, "unit": "TFLOP/s",
+    roofline = {"bound": "fp64", "kernel": "esb_physics_kernel<8>" if args.engine == "gm_ls" else "esb_physics_kernel", "achieved": achieved, "peak": fp64_fma, "unit": "TFLOP/s",
                 "frac": (achieved / fp64_fma) if achieved else None, "traffic": None,
                 "peak_source": "measured live: register-resident DFMA loop (EsbProbePeak); MEASURED_PEAKS.json holds no FP64 figure",
                 "peak_unfused_mul_add": fp64_sep,
@@ -313,7 +337,7 @@ def main():
     L = r["taps"][0]
     samples_total = args.steps * (r["b"].samples_for(steps))
     fir_ms = r["kms"][2]
-    fir_flops = 2.0 * L * 2 * samples_total * n
+    fir_flops = 2.0 * L * len(r["taps"]) * samples_total * n
     hbm_peak = peaks.get("hbm_gbs")
     stream_bytes = n * args.steps * (steps * 2 * 8 * 2 + r["b"].samples_for(steps) * (2 * 4 * 3 + 2 * 4 * 2 + 2))
     extra = {
@@ -327,14 +351,15 @@ def main():
         "kernel_ms": dict(zip(["physics", "synth_pre", "fir", "synth_post"], r["kms"])),
     }
     cpu = None
-    if not args.no_cpu_baseline and world == 1:
+    if not args.no_cpu_baseline and world == 1 and args.engine == "gm_ls":
         cores = os.cpu_count() or 1
         one_pass, engine_seconds = cpu_run(r["blob"], r["ir"], cores, args.cpu_sim_seconds, max_taps=max(args.ir_taps, 0))
         t = one_pass()
         cpu = {"value": engine_seconds / t, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"{cores} instances of the same grid x {args.cpu_sim_seconds} s engine time, one oracle instance per host thread"}
     line = {
-        "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "metric": METRIC if args.engine == "gm_ls" else "aggregate simulated engine-seconds per wall-second (" + args.engine + ")",
+        "value": r["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": r["ms_total"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
         "config": {"workload": workload_name(args),
