@@ -744,6 +744,8 @@ def to_preset(interp, source_script=""):
     e = interp.engine
     if not e["crankshafts"] or not e["banks"]:
         raise MrError("the engine has no crankshaft or no cylinder bank")
+    if e["throttle"].get("governor"):
+        raise MrError("governor throttle (es/objects/objects.mr governor) is not supported by the batched physics: only direct_throttle_linkage")
     exhausts, intakes = [], []
     banks_json, chambers, firing = [], [], []
     posts = e["ignition"]["posts"] if e["ignition"] else []

