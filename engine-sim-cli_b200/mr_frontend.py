@@ -384,6 +384,8 @@ class Interpreter:
         for st in stmts:
             if st[0] == "decl":
                 fs.pending[st[2]] = st
+            else:
+                fs.stmts.append(st)       # top-level calls, e.g. `main()` / `run()`: the script's entry point
         return fs
 
     # instantiation -------------------------------------------------------------------------
@@ -483,10 +485,12 @@ class Interpreter:
     # entry point ---------------------------------------------------------------------------
     def run(self, script_path, entry="main"):
         fs = self.load(script_path)
-        nd = fs.find_def(entry)
-        if nd is None:
-            raise MrError(f"{script_path}: no '{entry}' node")
-        self.instantiate(entry, [], fs)
+        for st in fs.stmts:                 # the file's own top-level calls are its entry point ...
+            self.eval(st[1], fs)
+        if self.engine is None:             # ... otherwise the conventional `main` node
+            if fs.find_def(entry) is None:
+                raise MrError(f"{script_path}: no top-level call and no '{entry}' node")
+            self.instantiate(entry, [], fs)
         if self.engine is None:
             raise MrError(f"{script_path}: the script never calls set_engine()")
         return self

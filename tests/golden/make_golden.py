@@ -40,6 +40,7 @@ SCRIPTS = {
     "lfa_v10": "es/engines/atg-video-2/10_lfa_v10.mr",
     "merlin_v12": "es/engines/atg-video-2/11_merlin_v12.mr",
     "hayabusa_i4": "es/engines/atg-video-1/04_hayabusa.mr",
+    "default_v8": "es/main.mr",   # the bridge's default script (BASELINE config 1): main.mr -> v8_engine.mr "Simple V8"
 }
 
 
