@@ -20,6 +20,7 @@ struct EngineSimOpaque {
     std::deque<int16_t> computed; // every sample the device has produced and nobody has read yet
     size_t released = 0;          // how many of them renderAudio() has moved into the audio buffer
     std::vector<int16_t> scratch;
+    std::vector<double> telemetry; // per-step telemetry of the last advance (keeps the exhaust-flow statistic current)
 };
 
 namespace {
@@ -291,7 +292,10 @@ static int advanceSingle(EngineSimHandle h, int steps) {
     h->b.samplesFor(steps, &n);
     if ((int)h->scratch.size() < n + 8) h->scratch.resize(n + 8);
     int produced = 0;
-    const int rc = h->b.render(steps, h->scratch.data(), nullptr, (long long)h->scratch.size(), &produced, nullptr, 0);
+    // per-step telemetry keeps the exhaust-flow total of the last step current: EngineSimGetStats().exhaustFlow is what
+    // the reference's CrankingController reads after every update (CrankingController.cpp:78-92)
+    h->telemetry.resize((size_t)steps * ESB_TELEMETRY_STRIDE);
+    const int rc = h->b.render(steps, h->scratch.data(), nullptr, (long long)h->scratch.size(), &produced, h->telemetry.data(), 1);
     if (rc != ESIM_SUCCESS) return rc;
     h->computed.insert(h->computed.end(), h->scratch.begin(), h->scratch.begin() + produced);
     return ESIM_SUCCESS;

@@ -59,7 +59,8 @@ public:
     void setThrottle(double x) override { if (h_) EngineSimSetThrottle(h_, x); }
     void setStarterMotor(bool on) override { if (h_) EngineSimSetStarterMotor(h_, on ? 1 : 0); }
     void setIgnition(bool on) override { if (h_) EngineSimSetIgnition(h_, on ? 1 : 0); }
-    void applyTransition(const TransitionDecision &d) override { // phase + starter together (ICombustionEngine.h)
+    void applyTransition(const TransitionDecision &d) override { // phase + starter together, only on a transition (BridgeSimulator.cpp:334-338)
+        if (!d.isTransition) return;
         phase_ = d.targetPhase;
         setStarterMotor(d.starterMotor);
     }

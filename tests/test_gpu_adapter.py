@@ -17,14 +17,20 @@ BIN = os.path.join(ROOT, "tests", "adapter", "_bin", "adapter_demo")
 REF_INC = "/root/reference/engine-sim-bridge/include"
 
 
+BIN_CRANK = os.path.join(ROOT, "tests", "adapter", "_bin", "cranking_demo")
+REF_CRANKING = "/root/reference/engine-sim-bridge/src/simulation/CrankingController.cpp"
+
+
 def build_adapter_demo():
     if not os.path.isdir(REF_INC):
-        return os.path.exists(BIN)
+        return os.path.exists(BIN) and os.path.exists(BIN_CRANK)
     os.makedirs(os.path.dirname(BIN), exist_ok=True)
     libdir = os.path.join(ROOT, "engine-sim-cli_b200")
-    subprocess.run(["g++", "-O2", "-std=c++17", "-I" + os.path.join(ROOT, "include"), "-I" + REF_INC,
-                    os.path.join(ROOT, "tests", "adapter", "adapter_demo.cpp"), "-L" + libdir, "-lenginesim_b200",
-                    "-Wl,-rpath,$ORIGIN/../../../engine-sim-cli_b200", "-o", BIN], check=True)
+    common = ["g++", "-O2", "-std=c++17", "-I" + os.path.join(ROOT, "include"), "-I" + REF_INC]
+    link = ["-L" + libdir, "-lenginesim_b200", "-Wl,-rpath,$ORIGIN/../../../engine-sim-cli_b200"]
+    subprocess.run(common + [os.path.join(ROOT, "tests", "adapter", "adapter_demo.cpp")] + link + ["-o", BIN], check=True)
+    # the reference's own CrankingController.cpp, compiled from where it lies (never copied), against the GPU engine
+    subprocess.run(common + [os.path.join(ROOT, "tests", "adapter", "cranking_demo.cpp"), REF_CRANKING] + link + ["-o", BIN_CRANK], check=True)
     return True
 
 
@@ -74,3 +80,37 @@ def test_adapter_matches_oracle(tmp_path):
         assert np.all(audio[t, n:] == 0)
     assert info["written"] == total
     assert abs(info["rpm"] - sim.telemetry()[0]) <= 1e-6 * abs(sim.telemetry()[0])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("throttle,ignition", [(0.3, 1), (0.3, 0)])
+def test_reference_cranking_controller_drives_the_gpu_engine(tmp_path, throttle, ignition):
+    """The reference's own CrankingController.cpp (compiled unmodified into tests/adapter/_bin/cranking_demo) starts the GPU
+    engine through ICombustionEngine; the vectorised controller of engine_sim_cli_b200/cranking.py must take exactly the
+    same decisions on the same engine: identical phase sequence, and RPM / exhaust-flow traces equal bit for bit."""
+    if not os.path.exists(BIN_CRANK):
+        pytest.skip("cranking_demo was not built (needs the reference headers at build time)")
+    import engine_sim_cli_b200 as esb
+    from engine_sim_cli_b200 import cranking as ck
+    irfile, ir = _ir_file(tmp_path)
+    ticks = 120
+    r = subprocess.run([BIN_CRANK, os.path.join(GOLDEN, "gm_ls.params.bin"), irfile, str(ticks), str(throttle), str(ignition)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    trace = np.array(json.loads(r.stdout))
+    blob = open(os.path.join(GOLDEN, "gm_ls.params.bin"), "rb").read()
+    b = esb.BatchSimulator(1, device=0, sim_freq=10000, seed=0)
+    b.load_params(blob)
+    for c in range(2):
+        b.set_impulse_response(c, ir, 0.001)
+    s = ck.BatchSession(b)
+    mine = []
+    for k in range(ticks):
+        s.tick(throttle=throttle, ignition=bool(ignition), starter_button=(k == 0), want_pcm=False)
+        mine.append([int(s.phase[0]), s.rpm[0], s.exhaust_flow[0]])
+    mine = np.array(mine)
+    assert np.array_equal(trace[:, 0], mine[:, 0])
+    assert np.array_equal(trace[:, 1], mine[:, 1]) and np.array_equal(trace[:, 2], mine[:, 2])
+    P = ck.EnginePhase
+    assert trace[0, 0] == P.Cranking
+    assert trace[-1, 0] == (P.Running if ignition else P.Cranking)
