@@ -18,12 +18,14 @@ REF_INC = "/root/reference/engine-sim-bridge/include"
 
 
 BIN_CRANK = os.path.join(ROOT, "tests", "adapter", "_bin", "cranking_demo")
+BIN_SYNCPULL = os.path.join(ROOT, "tests", "adapter", "_bin", "syncpull_demo")
+REF_SRC = "/root/reference/engine-sim-bridge/src"
 REF_CRANKING = "/root/reference/engine-sim-bridge/src/simulation/CrankingController.cpp"
 
 
 def build_adapter_demo():
     if not os.path.isdir(REF_INC):
-        return os.path.exists(BIN) and os.path.exists(BIN_CRANK)
+        return os.path.exists(BIN) and os.path.exists(BIN_CRANK) and os.path.exists(BIN_SYNCPULL)
     os.makedirs(os.path.dirname(BIN), exist_ok=True)
     libdir = os.path.join(ROOT, "engine-sim-cli_b200")
     common = ["g++", "-O2", "-std=c++17", "-I" + os.path.join(ROOT, "include"), "-I" + REF_INC]
@@ -31,6 +33,9 @@ def build_adapter_demo():
     subprocess.run(common + [os.path.join(ROOT, "tests", "adapter", "adapter_demo.cpp")] + link + ["-o", BIN], check=True)
     # the reference's own CrankingController.cpp, compiled from where it lies (never copied), against the GPU engine
     subprocess.run(common + [os.path.join(ROOT, "tests", "adapter", "cranking_demo.cpp"), REF_CRANKING] + link + ["-o", BIN_CRANK], check=True)
+    # the unmodified SyncPullStrategy + CrankingController + NullAudioHardwareProvider over the GPU engine
+    subprocess.run(common + [os.path.join(ROOT, "tests", "adapter", "syncpull_demo.cpp"), REF_SRC + "/strategy/SyncPullStrategy.cpp", REF_CRANKING,
+                             REF_SRC + "/hardware/NullAudioHardwareProvider.cpp", REF_SRC + "/common/ConsoleLogger.cpp"] + link + ["-o", BIN_SYNCPULL], check=True)
     return True
 
 
@@ -114,3 +119,29 @@ def test_reference_cranking_controller_drives_the_gpu_engine(tmp_path, throttle,
     P = ck.EnginePhase
     assert trace[0, 0] == P.Cranking
     assert trace[-1, 0] == (P.Running if ignition else P.Cranking)
+
+
+@pytest.mark.gpu
+def test_reference_sync_pull_strategy_pulls_the_gpu_engine(tmp_path):
+    """SURVEY.md 8(f) rank 4.  The reference's unmodified SyncPullStrategy (the audio-hardware callback path: render() ->
+    ISimulator::renderOnDemand, short read -> update(1/sr) + retry), CrankingController and NullAudioHardwareProvider run a
+    cold start of the GPU engine: every 512-frame hardware buffer is filled without a warning, the engine catches, the
+    stereo frames obey convertInt16ToStereoFloat (L = s*volume, R = s*convolutionLevel)."""
+    if not os.path.exists(BIN_SYNCPULL):
+        pytest.skip("syncpull_demo was not built (needs the reference sources at build time)")
+    import engine_sim_cli_b200 as esb
+    irfile, ir = _ir_file(tmp_path)
+    out = str(tmp_path / "pull.f32")
+    r = subprocess.run([BIN_SYNCPULL, os.path.join(GOLDEN, "gm_ls.params.bin"), irfile, "2.0", "0.3", out], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    info = json.loads(r.stdout)
+    assert info["warnings"] == 0 and info["errors"] == 0, r.stderr
+    assert info["lastFramesRendered"] == info["lastFramesRequested"] == 512
+    trace = np.array(info["trace"])
+    assert trace[0, 0] == 1 and trace[-1, 0] == 3 and trace[-1, 1] > 500      # Cranking at the first tick, Running at the end
+    pcm = np.fromfile(out, dtype=np.float32).reshape(-1, 2)
+    assert len(pcm) == info["frames"] >= 2 * 44100
+    assert np.array_equal(pcm[:, 0], pcm[:, 1])                               # volume == convolutionLevel == 0.5 by default
+    assert np.abs(pcm[-44100:, 0]).max() > 0.01 and np.abs(pcm).max() <= 0.5
+    s16 = pcm[:, 0] * 2 * 32768
+    assert np.array_equal(s16, np.round(s16))                                 # exact int16 / 32768 * 0.5
