@@ -163,8 +163,8 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &
         S[(size_t)ESB_GF_TOTAL_EXH_FLOW * n + inst] = s.totalExhaustFlow;
     }
     if (k.chainMode) {
-        if (k.roleP) storeCell(s.plenum, S, n, (size_t)(ESB_GF_PLENUM + 8 * k.shIn) * n + inst);
-        if (k.roleC) storeCell(s.collector, S, n, (size_t)(ESB_GF_COLLECTOR + 8 * k.shEx) * n + inst);
+        if (k.roleP && !k.helper) storeCell(s.plenum, S, n, (size_t)(ESB_GF_PLENUM + 8 * k.shIn) * n + inst);
+        if (k.roleC && !k.helper) storeCell(s.collector, S, n, (size_t)(ESB_GF_COLLECTOR + 8 * k.shEx) * n + inst);
     } else if (k.active) {
         // the first cylinder plumbed to an intake / exhaust system stores that replica
         const EsbEngineParams &P = D->P;
