@@ -62,6 +62,8 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &
     double *S = a.S;
     LaneConst k;
     loadLaneConst<G>(k, D, g.lane);
+    GasConst gcMem = k.gc;
+    k.gcp = &gcMem;
     const int cyl = k.active ? g.lane : 0;
     LaneState s;
     loadBody(s.crank, S, n, (size_t)ESB_GF_CRANK * n + inst);
