@@ -97,6 +97,7 @@ typedef struct EsbDeviceParams {
     double solverBeta, solverMinDelta;
     int32_t solverMaxIterations, fluidSteps;
     int32_t lanesPerInstance, pad;
+    int32_t valvePartner[16];      /* lane whose cylinder is a revolution out of phase with this lane's (deriveDeviceParams) */
     uint64_t seedBase;             /* instance i draws noise with seed seedBase + i */
 } EsbDeviceParams;
 
