@@ -329,10 +329,10 @@ def main():
                 "algorithmic_ops_per_instance_step": ops,
                 "avg_launch_ms": phys_ms / phys_n, "launches_timed": phys_n, "share_of_step": phys_ms / r["ms_total"]}
     # DRAM bytes of one launch from the committed ncu --set full capture (taken on a shorter launch: scaled per step)
-    prof = load_json(os.path.join(ROOT, "profiles", "physics_ncu_r01c.json"))
+    prof = load_json(os.path.join(ROOT, "profiles", "physics_ncu_r01d.json"))
     if prof and "dram_bytes_per_launch" in prof and prof.get("steps_in_launch"):
         roofline["traffic"] = prof["dram_bytes_per_launch"] / prof["steps_in_launch"] * per_launch_steps
-        roofline["traffic_source"] = "profiles/physics_ncu_r01c.json (dram__bytes_read.sum + dram__bytes_write.sum, scaled from a %d-step launch)" % prof["steps_in_launch"]
+        roofline["traffic_source"] = "profiles/physics_ncu_r01d.json (dram__bytes_read.sum + dram__bytes_write.sum, scaled from a %d-step launch)" % prof["steps_in_launch"]
     # secondary lines: convolution against the FP32 pipe, buffer streams against HBM
     L = r["taps"][0]
     samples_total = args.steps * (r["b"].samples_for(steps))
