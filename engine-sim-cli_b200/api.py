@@ -19,7 +19,8 @@ class EngineSimError(RuntimeError):
 
 
 def library_path():
-    return os.path.join(HERE, "libenginesim_b200.so")
+    # ESB_LIBRARY: developer override (instrumented builds of the same CUDA library, tools/phase_clocks.py)
+    return os.environ.get("ESB_LIBRARY") or os.path.join(HERE, "libenginesim_b200.so")
 
 
 class EsbControls(C.Structure):
@@ -59,7 +60,8 @@ def lib():
             "EsbBatchSetImpulseResponse": [vp, i32, vp, i32, flt, i32], "EsbBatchGetImpulseResponseTaps": [vp, i32, C.POINTER(i32)],
             "EsbBatchSetAudioParams": [vp, flt, flt, flt, flt, flt], "EsbBatchSetSolver": [vp, i32, dbl, dbl], "EsbBatchSetSineMode": [vp, i32],
             "EsbBatchSetControls": [vp, i32, i32, vp], "EsbBatchSetSchedule": [vp, i32, vp, vp, vp], "EsbBatchReset": [vp],
-            "EsbBatchRender": [vp, i32, vp, vp, i64, C.POINTER(i32), vp, i32], "EsbBatchSamplesFor": [vp, i32, C.POINTER(i32)],
+            "EsbBatchRender": [vp, i32, vp, vp, i64, C.POINTER(i32), vp, i32, i32], "EsbBatchTelemetrySamplesFor": [vp, i32, i32, C.POINTER(i32)],
+            "EsbBatchGetStepCount": [vp, C.POINTER(i64)], "EsbBatchSamplesFor": [vp, i32, C.POINTER(i32)],
             "EsbBatchGetDevicePcm": [vp, C.POINTER(vp), C.POINTER(i64), C.POINTER(i32)], "EsbBatchGetState": [vp, vp, C.POINTER(i32)],
             "EsbBatchGetLastStream": [vp, vp, i32, C.POINTER(i32)], "EsbBatchGetStats": [vp, i32, vp], "EsbBatchWriteWavs": [vp, C.c_char_p, C.c_char_p],
             "EsbBatchSetLaunchConfig": [vp, i32, i32], "EsbBatchGetLaunchCounts": [vp, vp],
@@ -224,20 +226,25 @@ class BatchSimulator:
             pcm = pcm_out if pcm_out is not None else np.zeros((self.n, max(m, 1)), dtype=np.int16)
         pcmf = np.zeros((self.n, max(m, 1)), dtype=np.float32) if want_float else None
         stride = pcm.shape[1] if pcm is not None else (pcmf.shape[1] if pcmf is not None else 0)
-        tel = None
+        tel, k = None, 0
         if telemetry_every:
-            k = (self._steps_done + n_steps) // telemetry_every - self._steps_done // telemetry_every
+            # the library's own step counter decides which steps are sampled (reset() / set_solver() / a reload restart it)
+            kk = C.c_int32()
+            self._check(lib().EsbBatchTelemetrySamplesFor(self.h, n_steps, telemetry_every, C.byref(kk)))
+            k = kk.value
             tel = np.zeros((max(k, 1), TELEMETRY_STRIDE, self.n))
         produced = C.c_int32()
-        self._check(lib().EsbBatchRender(self.h, n_steps, _ptr(pcm), _ptr(pcmf), stride, C.byref(produced), _ptr(tel), telemetry_every))
-        self._steps_done += n_steps
+        self._check(lib().EsbBatchRender(self.h, n_steps, _ptr(pcm), _ptr(pcmf), stride, C.byref(produced), _ptr(tel), telemetry_every,
+                                         tel.shape[0] if tel is not None else 0))
         n = produced.value
         if tel is not None:
-            k = self._steps_done // telemetry_every - (self._steps_done - n_steps) // telemetry_every
             tel = tel[:k]
         return (pcm[:, :n] if pcm is not None else None), (pcmf[:, :n] if pcmf is not None else None), tel
 
-    _steps_done = 0
+    def step_count(self):
+        out = C.c_int64()
+        self._check(lib().EsbBatchGetStepCount(self.h, C.byref(out)))
+        return out.value
 
     def device_pcm(self):
         ptr, stride, n = C.c_void_p(), C.c_int64(), C.c_int32()

@@ -131,6 +131,13 @@ int Batch::loadParams(const EsbEngineParams &p) {
     params = p;
     loaded = true;
     channels = p.exhaustSystemCount;
+    // a second load may change the row count (exhaust systems) and the engine's defaults: the convolution buffers are
+    // reallocated by reset() and the controls re-seeded from the new engine
+    if (device >= 0) cudaSetDevice(device);
+    if (stream) cudaStreamSynchronize(stream);
+    if (dX) { cudaFree(dX); dX = nullptr; }
+    if (dY) { cudaFree(dY); dY = nullptr; }
+    hCtl.clear();
     // applyLoadedEngineSettings (SimulatorFactory.cpp:63-71): engine's frequency unless the config overrides
     // (BridgeSimulator.cpp:496-504); synth noise / jitter / hf gain from the engine
     simFreq = (cfg.simulationFrequency > 0) ? (double)cfg.simulationFrequency : p.simulationFrequency;
@@ -196,6 +203,11 @@ int Batch::allocSynth() {
 
 int Batch::reset() {
     if (!loaded) { lastError = "no engine loaded"; return ESIM_ERROR_NOT_INITIALIZED; }
+    // K3 stages the samples of one physics step in shared memory (synth_kernels.cu): bound the resampling ratio
+    if (std::ceil((double)cfg.sampleRate / simFreq) + 1 > ESB_MAX_SAMPLES_PER_STEP) {
+        lastError = "sampleRate / simulationFrequency is larger than the synthesizer input stage supports (" + std::to_string(ESB_MAX_SAMPLES_PER_STEP - 1) + " samples per step)";
+        return ESIM_ERROR_INVALID_PARAMETER;
+    }
     ESB_CUDA(cudaSetDevice(device));
     deriveDeviceParams(params, simFreq, cfg.fluidSimulationSteps, solverMaxIt, solverMinDelta, solverBeta, cfg.seed, hostD);
     lanes = hostD.lanesPerInstance;
@@ -325,6 +337,12 @@ int Batch::setLaunchConfig(int blockThreads_, int stepsPerLaunch_) {
         blockThreads = blockThreads_;
     }
     if (stepsPerLaunch_ > 0 && stepsPerLaunch_ != stepsPerLaunch) {
+        if (loaded && samplesProduced != 0) {
+            // the convolution history lives in X: reallocating it would lose it, so a chunk can only grow before the first render
+            const double spStep = (double)cfg.sampleRate / simFreq;
+            const long long need = (long long)std::ceil(stepsPerLaunch_ * spStep) + 8;
+            if (need > chunkSamplesMax) { lastError = "stepsPerLaunch can only grow before the first render"; return ESIM_ERROR_INVALID_PARAMETER; }
+        }
         stepsPerLaunch = stepsPerLaunch_;
         if (loaded) {
             ESB_CUDA(cudaSetDevice(device));
@@ -332,11 +350,7 @@ int Batch::setLaunchConfig(int blockThreads_, int stepsPerLaunch_) {
             if (dStream) { cudaFree(dStream); dStream = nullptr; }
             ESB_CUDA(cudaMalloc(&dStream, (size_t)stepsPerLaunch * channels * nInst * sizeof(double)));
             streamCapSteps = stepsPerLaunch;
-            // keep the convolution history: reallocating X would lose it, so only grow when nothing was produced yet
             if (samplesProduced == 0) return allocSynth();
-            const double spStep = (double)cfg.sampleRate / simFreq;
-            const long long need = (long long)std::ceil(stepsPerLaunch * spStep) + 8;
-            if (need > chunkSamplesMax) { lastError = "stepsPerLaunch can only grow before the first render"; return ESIM_ERROR_INVALID_PARAMETER; }
         }
     }
     return ESIM_SUCCESS;
@@ -461,7 +475,7 @@ int Batch::ensurePcm(long long samples, bool wantFloat) {
     return ESIM_SUCCESS;
 }
 
-int Batch::render(int nSteps, int16_t *pcm, float *pcmFloat, long long hostStride, int *outSamples, double *telemetry, int telEvery) {
+int Batch::render(int nSteps, int16_t *pcm, float *pcmFloat, long long hostStride, int *outSamples, double *telemetry, int telEvery, long long telCapacity) {
     if (!loaded) { lastError = "no engine loaded"; return ESIM_ERROR_NOT_INITIALIZED; }
     if (nSteps < 0) { lastError = "nSteps must be non-negative"; return ESIM_ERROR_INVALID_PARAMETER; }
     ESB_CUDA(cudaSetDevice(device));
@@ -479,6 +493,10 @@ int Batch::render(int nSteps, int16_t *pcm, float *pcmFloat, long long hostStrid
     if (telemetry && telEvery > 0 && !sineMode) {
         telBase = stepCount / telEvery;
         telCount = (stepCount + nSteps) / telEvery - telBase;
+        if (telCapacity >= 0 && telCount > telCapacity) {
+            lastError = "telemetry buffer holds " + std::to_string(telCapacity) + " samples, this render produces " + std::to_string(telCount);
+            return ESIM_ERROR_INVALID_PARAMETER;
+        }
         const size_t bytes = (size_t)std::max<long long>(telCount, 1) * ESB_TELEMETRY_STRIDE * nInst * sizeof(double);
         if (bytes > telBytes) {
             ESB_CUDA(cudaStreamSynchronize(stream));

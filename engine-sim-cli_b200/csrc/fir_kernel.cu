@@ -169,12 +169,10 @@ cudaError_t esbLaunchFir(const EsbFirArgs &a, cudaStream_t stream) {
     if (a.Lp % KT != 0 || a.rows % ROWS != 0 || (a.hist + 1) % 4 != 0 || (a.n0 - a.xOrigin) % 4 != 0 || a.xStride % 4 != 0 || a.yStride % 4 != 0 ||
         a.rowsPerIr % ROWS != 0)
         return cudaErrorInvalidValue;
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(esb_fir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-        if (e != cudaSuccess) return e;
-        configured = true;
-    }
+    // The attribute belongs to the (function, device) pair and a process may hold batches on several devices,
+    // from several host threads: set it before every launch (a host-side table update, no device work).
+    cudaError_t e = cudaFuncSetAttribute(esb_fir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e != cudaSuccess) return e;
     dim3 grid((unsigned)((a.count + T - 1) / T), (unsigned)(a.rows / ROWS));
     esb_fir_kernel<<<grid, WARPS * 32, SMEM_BYTES, stream>>>(a);
     return cudaGetLastError();

@@ -27,6 +27,10 @@ __global__ void __launch_bounds__(256, (MINB >= 7 ? 2 : 1)) esb_physics_kernel(R
     Group<G> g;
     g.lane = laneInWarp % G;
     g.mask = (G >= 32) ? 0xffffffffu : (((1u << G) - 1u) << (laneInWarp & ~(G - 1)));
+#ifdef ESB_PHASE_CLOCKS
+    g.clkOn = blockIdx.x == 0 && threadIdx.x == 0;
+    g.clkLast = clock64();
+#endif
     runInstance<G>(a, inst, live, g);
 }
 
@@ -70,3 +74,11 @@ cudaError_t esbLaunchPhysics(const esbk::RunArgs &a, int lanes, int blockThreads
     default: return cudaErrorInvalidValue;
     }
 }
+
+#ifdef ESB_PHASE_CLOCKS
+extern "C" int EsbDebugPhaseClocks(unsigned long long *out, int reset) {
+    if (cudaMemcpyFromSymbol(out, esbk::esbPhaseClk, sizeof(unsigned long long) * 32) != cudaSuccess) return -1;
+    if (reset) { unsigned long long z[32] = {0}; cudaMemcpyToSymbol(esbk::esbPhaseClk, z, sizeof z); }
+    return 0;
+}
+#endif

@@ -121,7 +121,9 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &
         // DelayFilter::fast_f — the value leaving the ring this step is known before the step
         const double delayed = k.active ? ring[(size_t)s.delayPos * ringStride] : 0.0;
         double out[ESB_MAX_EXHAUST];
-        const double exhaustFlow = simulateStep<G>(s, k, D, ctl, g, seed, delayed, out, sample);
+        // exhaust-flow total: on telemetry steps, and on the last step of every launch so that the stored statistic
+        // (EsbBatchGetStats().exhaustFlow, BridgeSimulator::getStats) is current whatever the telemetry interval
+        const double exhaustFlow = simulateStep<G>(s, k, D, ctl, g, seed, delayed, out, sample || step + 1 == a.nSteps);
         if (k.active) {
             if (live) ring[(size_t)s.delayPos * ringStride] = exhaustFlow;
             s.delayPos = (s.delayPos + 1 == k.delayLen) ? 0 : s.delayPos + 1;

@@ -26,7 +26,9 @@ __device__ __forceinline__ double inputDistance(double s1, double s0, double buf
 }
 
 constexpr int TILE = 32;
-constexpr int STAGE = 40;  // staged samples per row before a flush (32 + up to 5 new + slack)
+// staged samples per row: fewer than TILE left over from the last flush + the samples one physics step writes.
+// ESB_MAX_SAMPLES_PER_STEP (kernels.h) bounds the latter; Batch::reset() rejects sampleRate / simFreq ratios beyond it.
+constexpr int STAGE = TILE + ESB_MAX_SAMPLES_PER_STEP;
 
 // K3 -------------------------------------------------------------------------------------
 // grid: (nInstPad / 32, channels); block: 32 threads (one warp); lane = instance within the block
@@ -105,7 +107,7 @@ __global__ void __launch_bounds__(32) esb_synth_pre_kernel(EsbPreArgs a) {
         writeIndex = (writeIndex + written) % (long long)bufferSize;
         lastInputSampleOffset = inputWriteOffset;
         staged += written;
-        if (staged >= TILE) { // flush one 32-sample tile, transposed: lane = sample
+        while (staged >= TILE) { // flush 32-sample tiles, transposed: lane = sample
             __syncwarp();
             const long long col = a.hist + (flushed - a.xOrigin) + lane;
             for (int r = 0; r < TILE; ++r) a.X[(rowBlock + r) * a.xStride + col] = stage[r][lane];

@@ -32,6 +32,8 @@ void orc_sim_set_audio_params(void *h, float convolution, float dF_F_mix, float 
     AudioParameters &a = ((Simulator *)h)->synth.ap;
     a.convolution = convolution; a.dF_F_mix = dF_F_mix; a.inputSampleNoise = inputSampleNoise; a.airNoise = airNoise; a.volume = volume;
 }
+// output sample rate of the synthesizer (before the first step; the reference's tests also run at 48 kHz)
+void orc_sim_set_sample_rate(void *h, int rate) { ((Simulator *)h)->synth.audioSampleRate = rate; ((Simulator *)h)->sampleRate = rate; }
 void orc_sim_set_fir_mode(void *h, int mode) { ((Simulator *)h)->synth.firMode = mode; }
 void orc_sim_set_solver(void *h, int maxIterations, double minDelta, double beta) {
     SolverConfig &c = ((Simulator *)h)->engine.solver;
