@@ -371,7 +371,7 @@ int Batch::advanceChunk(int nSteps, double *telDev, int telEvery, long long telB
         a.nKeys = nKeys; a.keyStep = dKeyStep; a.keyThrottle = dKeyThr; a.keyDynoSpeed = dKeyDyno;
         a.stream = dStream; a.channels = channels; a.telemetry = telDev; a.telemetryEvery = telEvery; a.telemetryBase = telBase;
         markBegin(0);
-        ESB_CUDA(esbLaunchPhysics(a, lanes, blockThreads, instPerWarp, kernelVariant, stream));
+        ESB_CUDA(esbLaunchPhysics(a, hostD, blockThreads, instPerWarp, kernelVariant, stream));
         markEnd();
         ++launchCounts[0];
     }

@@ -83,6 +83,54 @@ typedef struct EsbCylDerived {
     int32_t delayLen, pad;
 } EsbCylDerived;
 
+/* ---- gas network: cells, operation tables and the slot schedule of one simulation step ----
+ *
+ * The fluid part of a step (fluidSimulationSteps x {Intake::process, CombustionChamber::flow per cylinder,
+ * ExhaustSystem::process}) is a fixed list of operations on gas cells: two-cell exchanges (GasSystem::flow),
+ * single-cell relaxations (dissipateExcessVelocity + updateVelocity) and the blow-by of a chamber.  Two
+ * operations that touch no common cell commute exactly, so the only order that matters is the order in which
+ * each cell sees its operations.  The host lists the operations of a whole step in the reference's order,
+ * derives the per-cell dependencies and packs the operations into SLOTS (gas_schedule.cpp); the kernel walks
+ * the slots, every lane pair (exchange slots) or lane (relax / blow-by slots) of an instance executing the
+ * operation the slot gives it on cells that live in shared memory.  Same operations on the same values as the
+ * sequential form, hence the same bits.
+ *
+ * Cell ids: chamber c = 3c, intake runner c = 3c + 1, exhaust runner c = 3c + 2, plenum i = 3N + i,
+ * collector e = 3N + nIntakes + e; then the constant cells (never stored): the fuel-air atmosphere of intake i,
+ * the plain-air atmosphere the collectors blow into, and a cell at rest for idle lane pairs. */
+#define ESB_GAS_MAX_CELLS (3 * ESB_MAX_CYL + ESB_MAX_INTAKE + ESB_MAX_EXHAUST)
+#define ESB_GAS_MAX_CONST (ESB_MAX_INTAKE + 2)
+#define ESB_GAS_MAX_EXCH (4 * ESB_MAX_CYL + 2 * ESB_MAX_INTAKE + ESB_MAX_EXHAUST + 1)
+#define ESB_GAS_MAX_RELAX (2 * ESB_MAX_CYL + ESB_MAX_INTAKE + ESB_MAX_EXHAUST)
+#define ESB_GAS_MAX_SLOTS 640
+#define ESB_GAS_CELL_STRIDE 10 /* doubles per cell in shared memory: 8 used, 80-byte pitch (16-byte aligned, odd multiple of 16) */
+#define ESB_GAS_IDLE 0xff      /* slot entry: this lane (pair) has nothing to do */
+enum EsbGasSlotType { ESB_SLOT_EXCHANGE = 0, ESB_SLOT_RELAX = 1, ESB_SLOT_BLOWBY = 2 };
+
+typedef struct EsbGasExchange {   /* GasSystem::flow(FlowParameters) between cell0 and cell1 */
+    double kConst;                /* flow constant when kSource < 0 */
+    double dirx, diry, area0, area1;
+    int32_t cell0, cell1;
+    int32_t kSource;              /* index into the per-step k array: valve k of a cylinder (c intake, N + c exhaust), inlet k of intake i (2N + i) */
+    int32_t flowCylinder;         /* >= 0: the exhaust-valve exchange of that cylinder; its flow goes into the step's exhaust-flow total */
+} EsbGasExchange;
+
+typedef struct EsbGasRelax {      /* dissipateExcessVelocity + updateVelocity of one cell */
+    double beta, width, height, dx, dy;
+    int32_t cell, pad;
+} EsbGasRelax;
+
+typedef struct EsbGasNet {
+    int32_t nCells, nConst, nExchange, nRelax;
+    int32_t nSlots, entriesPerSlot;   /* entriesPerSlot = lanes per instance */
+    int32_t pairsPerSlot, split;      /* exchange capacity of a slot; split = two lanes share one exchange */
+    EsbGasExchange exchange[ESB_GAS_MAX_EXCH];   /* the last one (index nExchange) is the idle exchange between two cells at rest */
+    EsbGasRelax relax[ESB_GAS_MAX_RELAX];
+    double constCells[ESB_GAS_MAX_CONST][8];
+    uint8_t slotType[ESB_GAS_MAX_SLOTS];
+    uint16_t slotOps[ESB_GAS_MAX_SLOTS * 16];    /* [slot][entry]: operation index | substep << 8 ; ESB_GAS_IDLE in the low byte = idle */
+} EsbGasNet;
+
 typedef struct EsbDeviceParams {
     EsbEngineParams P;
     EsbCylDerived cd[ESB_MAX_CYL];
@@ -97,8 +145,8 @@ typedef struct EsbDeviceParams {
     double solverBeta, solverMinDelta;
     int32_t solverMaxIterations, fluidSteps;
     int32_t lanesPerInstance, pad;
-    int32_t valvePartner[16];      /* lane whose cylinder is a revolution out of phase with this lane's (deriveDeviceParams) */
     uint64_t seedBase;             /* instance i draws noise with seed seedBase + i */
+    EsbGasNet gas;
 } EsbDeviceParams;
 
 #endif

@@ -33,5 +33,7 @@ int lanesForCylinders(int n);
 void deriveDeviceParams(const EsbEngineParams &P, double simFreq, int fluidSteps, int maxIterations, double minDelta, double beta,
                         uint64_t seedBase, EsbDeviceParams &D);
 void initialStateColumn(const EsbDeviceParams &D, std::vector<double> &col);
+// gas_schedule.cpp — gas-network tables and the slot schedule of one step (called by deriveDeviceParams)
+void buildGasNet(const EsbEngineParams &P, EsbDeviceParams &D);
 
 } // namespace esb

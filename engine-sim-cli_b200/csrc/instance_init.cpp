@@ -61,34 +61,6 @@ void deriveDeviceParams(const EsbEngineParams &P, double simFreq, int fluidSteps
     D.invCrankMass = 1.0 / (P.crankMass + P.flywheelMass);
     D.invCrankInertia = 1.0 / P.crankMomentOfInertia;
     D.invVehMass = 1.0; D.invVehInertia = 1.0; // SimulatorInitHelpers.cpp:25-28
-    {
-        // Valve-slot lane pairs (physics_core.cuh valveExchangePaired): a cylinder is paired with the one a crank revolution
-        // away in the four-stroke cycle, whose valves are shut while its own are open; lanes left over pair up in order.
-        // Any pairing gives the same results (a pair with both valves open falls back to separate exchanges), only the
-        // speed depends on it.
-        const int G = D.lanesPerInstance, N = P.cylinderCount;
-        int partner[16];
-        for (int l = 0; l < 16; ++l) partner[l] = -1;
-        auto phase = [&](int c) { return P.cyl[c].intakeLobeCenterline - P.cyl[c].intakeCamAdvance; };
-        for (int c = 0; c < N && c < G; ++c) {
-            if (partner[c] >= 0) continue;
-            int best = -1; double bestD = 0.35; // 20 degrees
-            for (int t = c + 1; t < N && t < G; ++t) {
-                if (partner[t] >= 0) continue;
-                double d = std::fmod(phase(t) - phase(c) - 2.0 * kPi, 4.0 * kPi);
-                if (d < 0) d += 4.0 * kPi;
-                if (d > 2.0 * kPi) d = 4.0 * kPi - d;
-                if (d < bestD) { bestD = d; best = t; }
-            }
-            if (best >= 0) { partner[c] = best; partner[best] = c; }
-        }
-        int prev = -1;
-        for (int l = 0; l < G; ++l) {
-            if (partner[l] >= 0) continue;
-            if (prev < 0) prev = l; else { partner[l] = prev; partner[prev] = l; prev = -1; }
-        }
-        for (int l = 0; l < 16; ++l) D.valvePartner[l] = (l < G && partner[l] >= 0) ? partner[l] : l;
-    }
     const int dof = 5;
     const double g = 1.0 + 2.0 / dof;
     D.hcr = g;
@@ -136,6 +108,7 @@ void deriveDeviceParams(const EsbEngineParams &P, double simFreq, int fluidSteps
         if (len > ESB_MAX_DELAY) len = ESB_MAX_DELAY;
         d.delayLen = len;
     }
+    buildGasNet(P, D);
 }
 
 // One column (ESB_STATE_FIELDS doubles) of the state block: the state every instance starts from.

@@ -4,9 +4,10 @@
 #include <cstdint>
 
 namespace esbk { struct RunArgs; }
+struct EsbDeviceParams;
 
-// K1+K2: physics (physics_kernel.cu)
-cudaError_t esbLaunchPhysics(const esbk::RunArgs &a, int lanes, int blockThreads, int instPerWarp, int variant, cudaStream_t stream);
+// K1+K2: physics (physics_kernel.cu).  hostD: the host copy of the parameter block a.D points to (lane count, shared-memory layout)
+cudaError_t esbLaunchPhysics(const esbk::RunArgs &a, const EsbDeviceParams &hostD, int blockThreads, int instPerWarp, int variant, cudaStream_t stream);
 
 // Synthesizer clock: the 10 kHz -> 44.1 kHz resampler bookkeeping of Synthesizer::writeInput
 // (archive/PHYSICS_ANALYSIS.md:39-55), identical for every instance, so the host tracks it.

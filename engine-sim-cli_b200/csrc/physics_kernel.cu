@@ -1,9 +1,9 @@
 // physics_kernel.cu — K1+K2 fused: the batched physics kernel (sm_100a).
 //
 // One lane group per engine instance (G = 1, 2, 4, 8 or 16 lanes, the next power of two >= the
-// cylinder count), 32/G instances per warp, state in registers for the whole launch; see
-// physics_core.cuh for the algorithm and its mapping onto lanes and physics_run.cuh for the
-// launch-level loop.  FP64 throughout, built with -fmad=false so every operation rounds as in
+// cylinder count), 32/G instances per warp, rigid-body state in registers and gas cells in shared
+// memory for the whole launch; see physics_core.cuh for the algorithm and its mapping onto lanes
+// and physics_run.cuh for the launch-level loop and the shared-memory layout.  FP64 throughout, built with -fmad=false so every operation rounds as in
 // the reference's operation order.
 #include "physics_run.cuh"
 #include "kernels.h"
@@ -24,6 +24,13 @@ __global__ void __launch_bounds__(256, (MINB >= 7 ? 2 : 1)) esb_physics_kernel(R
     int inst = warp * instPerWarp + slot;
     const bool live = slot < instPerWarp && inst < a.nInst;
     if (!live) inst = a.nInst - 1;
+    // shared memory: the gas-network tables once per block, then one region per lane group
+    extern __shared__ __align__(16) unsigned char esbSmem[];
+    const EsbGasNet &gn = a.D->gas;
+    const GasSmemLayout L = gasSmemLayout(gn, a.D->P.cylinderCount, a.D->P.intakeCount, a.D->fluidSteps, blockDim.x / G);
+    gasTablesToShared(esbSmem, L, gn, threadIdx.x, blockDim.x);
+    __syncthreads();
+    const GasView view = gasViewAt(esbSmem, L, gn, threadIdx.x / G);
     Group<G> g;
     g.lane = laneInWarp % G;
     g.mask = (G >= 32) ? 0xffffffffu : (((1u << G) - 1u) << (laneInWarp & ~(G - 1)));
@@ -31,7 +38,7 @@ __global__ void __launch_bounds__(256, (MINB >= 7 ? 2 : 1)) esb_physics_kernel(R
     g.clkOn = blockIdx.x == 0 && threadIdx.x == 0;
     g.clkLast = clock64();
 #endif
-    runInstance<G>(a, inst, live, g);
+    runInstance<G>(a, inst, live, g, view);
 }
 
 } // namespace esbk
@@ -50,27 +57,37 @@ cudaError_t esbLaunchFastArCheck(int op, int n, const double *a, const double *b
     return cudaGetLastError();
 }
 
+template <int G, int MINB>
+static cudaError_t launchKernel(const esbk::RunArgs &a, int grid, int blockThreads, int instPerWarp, size_t smem, cudaStream_t stream) {
+    // per (function, device): set before every launch, a process may drive several devices
+    cudaError_t e = cudaFuncSetAttribute(esbk::esb_physics_kernel<G, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    esbk::esb_physics_kernel<G, MINB><<<grid, blockThreads, smem, stream>>>(a, instPerWarp);
+    return cudaGetLastError();
+}
+
 template <int G>
-static cudaError_t launchG(const esbk::RunArgs &a, int blockThreads, int instPerWarp, int variant, cudaStream_t stream) {
+static cudaError_t launchG(const esbk::RunArgs &a, const EsbDeviceParams &hostD, int blockThreads, int instPerWarp, int variant, cudaStream_t stream) {
     const int full = 32 / G;
     if (instPerWarp <= 0 || instPerWarp > full) instPerWarp = full;
     const long long warps = ((long long)a.nInst + instPerWarp - 1) / instPerWarp;
     const int wpb = blockThreads / 32;
     const int grid = (int)((warps + wpb - 1) / wpb);
-    if (G == 8 && variant == 1) esbk::esb_physics_kernel<G, (G == 8 ? 7 : 4)><<<grid, blockThreads, 0, stream>>>(a, instPerWarp);
-    else if (G == 8 && variant == 2) esbk::esb_physics_kernel<G, (G == 8 ? 8 : 4)><<<grid, blockThreads, 0, stream>>>(a, instPerWarp);
-    else esbk::esb_physics_kernel<G, 4><<<grid, blockThreads, 0, stream>>>(a, instPerWarp);
-    return cudaGetLastError();
+    const esbk::GasSmemLayout L = esbk::gasSmemLayout(hostD.gas, hostD.P.cylinderCount, hostD.P.intakeCount, hostD.fluidSteps, blockThreads / G);
+    if (L.total > 227u * 1024u) return cudaErrorInvalidConfiguration;
+    if (G == 8 && variant == 1) return launchKernel<G, (G == 8 ? 7 : 4)>(a, grid, blockThreads, instPerWarp, L.total, stream);
+    if (G == 8 && variant == 2) return launchKernel<G, (G == 8 ? 8 : 4)>(a, grid, blockThreads, instPerWarp, L.total, stream);
+    return launchKernel<G, 4>(a, grid, blockThreads, instPerWarp, L.total, stream);
 }
 
-cudaError_t esbLaunchPhysics(const esbk::RunArgs &a, int lanes, int blockThreads, int instPerWarp, int variant, cudaStream_t stream) {
+cudaError_t esbLaunchPhysics(const esbk::RunArgs &a, const EsbDeviceParams &hostD, int blockThreads, int instPerWarp, int variant, cudaStream_t stream) {
     if (blockThreads % 32 != 0 || blockThreads < 32 || blockThreads > 256) return cudaErrorInvalidValue;
-    switch (lanes) {
-    case 1: return launchG<1>(a, blockThreads, instPerWarp, variant, stream);
-    case 2: return launchG<2>(a, blockThreads, instPerWarp, variant, stream);
-    case 4: return launchG<4>(a, blockThreads, instPerWarp, variant, stream);
-    case 8: return launchG<8>(a, blockThreads, instPerWarp, variant, stream);
-    case 16: return launchG<16>(a, blockThreads, instPerWarp, variant, stream);
+    switch (hostD.lanesPerInstance) {
+    case 1: return launchG<1>(a, hostD, blockThreads, instPerWarp, variant, stream);
+    case 2: return launchG<2>(a, hostD, blockThreads, instPerWarp, variant, stream);
+    case 4: return launchG<4>(a, hostD, blockThreads, instPerWarp, variant, stream);
+    case 8: return launchG<8>(a, hostD, blockThreads, instPerWarp, variant, stream);
+    case 16: return launchG<16>(a, hostD, blockThreads, instPerWarp, variant, stream);
     default: return cudaErrorInvalidValue;
     }
 }

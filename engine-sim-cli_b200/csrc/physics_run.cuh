@@ -27,6 +27,55 @@ struct RunArgs {
     long long telemetryBase; // global index of the sample stored at telemetry[0]
 };
 
+// Shared-memory carve-up of one block: the gas-network tables (one copy per block), then one region per lane group
+// (instance) with its cells, its per-step flow constants and its exhaust-valve flow record.  Offsets in bytes, 16-byte aligned.
+struct GasSmemLayout { unsigned offType, offOps, offExchange, offRelax, offConst, offInst, instBytes, kStepDoubles, total; };
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+inline GasSmemLayout gasSmemLayout(const EsbGasNet &gn, int nCyl, int nIntakes, int fluidSteps, int groups) {
+    auto up = [](unsigned v) { return (v + 15u) & ~15u; };
+    GasSmemLayout L;
+    L.offType = 0;
+    L.offOps = up((unsigned)gn.nSlots);
+    L.offExchange = L.offOps + up((unsigned)(gn.nSlots * gn.entriesPerSlot * sizeof(uint16_t)));
+    L.offRelax = L.offExchange + up((unsigned)((gn.nExchange + 1) * sizeof(EsbGasExchange)));
+    L.offConst = L.offRelax + up((unsigned)(gn.nRelax * sizeof(EsbGasRelax)));
+    L.offInst = L.offConst + up((unsigned)(gn.nConst * ESB_GAS_CELL_STRIDE * sizeof(double)));
+    L.kStepDoubles = (unsigned)((2 * nCyl + nIntakes + 1) & ~1);
+    L.instBytes = up((unsigned)((gn.nCells * ESB_GAS_CELL_STRIDE + L.kStepDoubles + fluidSteps * nCyl) * sizeof(double))) + 16u;   // +16: neighbours start one bank group apart
+    L.total = L.offInst + L.instBytes * (unsigned)groups;
+    return L;
+}
+// The view of group `group` over a block's shared memory (or, in the host emulation, over plain arrays laid out the same way).
+ESB_DEV GasView gasViewAt(unsigned char *base, const GasSmemLayout &L, const EsbGasNet &gn, int group) {
+    GasView v;
+    v.slotType = base + L.offType;
+    v.slotOps = reinterpret_cast<const uint16_t *>(base + L.offOps);
+    v.exchange = reinterpret_cast<const EsbGasExchange *>(base + L.offExchange);
+    v.relax = reinterpret_cast<const EsbGasRelax *>(base + L.offRelax);
+    v.constCells = reinterpret_cast<const double *>(base + L.offConst);
+    v.cells = reinterpret_cast<double *>(base + L.offInst + (size_t)L.instBytes * group);
+    v.kStep = v.cells + gn.nCells * ESB_GAS_CELL_STRIDE;
+    v.flows = v.kStep + L.kStepDoubles;
+    v.nSlots = gn.nSlots; v.entries = gn.entriesPerSlot; v.nCells = gn.nCells; v.nExchange = gn.nExchange;
+    return v;
+}
+// Copies the tables into the block's shared memory: element i of each table by thread (tid + k * nThreads).
+ESB_DEV void gasTablesToShared(unsigned char *base, const GasSmemLayout &L, const EsbGasNet &gn, int tid, int nThreads) {
+    for (int i = tid; i < gn.nSlots; i += nThreads) base[L.offType + i] = gn.slotType[i];
+    uint16_t *ops = reinterpret_cast<uint16_t *>(base + L.offOps);
+    for (int i = tid; i < gn.nSlots * gn.entriesPerSlot; i += nThreads) ops[i] = gn.slotOps[(i / gn.entriesPerSlot) * 16 + (i % gn.entriesPerSlot)];
+    int *ex = reinterpret_cast<int *>(base + L.offExchange);
+    const int *exSrc = reinterpret_cast<const int *>(gn.exchange);
+    for (int i = tid; i < (int)((gn.nExchange + 1) * sizeof(EsbGasExchange) / sizeof(int)); i += nThreads) ex[i] = exSrc[i];
+    int *rx = reinterpret_cast<int *>(base + L.offRelax);
+    const int *rxSrc = reinterpret_cast<const int *>(gn.relax);
+    for (int i = tid; i < (int)(gn.nRelax * sizeof(EsbGasRelax) / sizeof(int)); i += nThreads) rx[i] = rxSrc[i];
+    double *cc = reinterpret_cast<double *>(base + L.offConst);
+    for (int i = tid; i < gn.nConst * 8; i += nThreads) cc[(i / 8) * ESB_GAS_CELL_STRIDE + (i % 8)] = gn.constCells[i / 8][i % 8];
+}
+
 ESB_DEV void loadBody(Body &b, const double *S, size_t stride, size_t base) {
     b.px = S[base]; b.py = S[base + stride]; b.th = S[base + 2 * stride];
     b.vx = S[base + 3 * stride]; b.vy = S[base + 4 * stride]; b.w = S[base + 5 * stride];
@@ -35,11 +84,15 @@ ESB_DEV void storeBody(const Body &b, double *S, size_t stride, size_t base) {
     S[base] = b.px; S[base + stride] = b.py; S[base + 2 * stride] = b.th;
     S[base + 3 * stride] = b.vx; S[base + 4 * stride] = b.vy; S[base + 5 * stride] = b.w;
 }
-ESB_DEV void loadCell(Cell &c, const double *S, size_t stride, size_t base) {
+// gas cells: state block (8 strided fields) <-> the instance's shared-memory cell
+ESB_DEV void loadCell(double *cellMem, const double *S, size_t stride, size_t base) {
+    Cell c;
     c.n = S[base]; c.E = S[base + stride]; c.V = S[base + 2 * stride]; c.mx = S[base + 3 * stride];
     c.my = S[base + 4 * stride]; c.pf = S[base + 5 * stride]; c.pi = S[base + 6 * stride]; c.po = S[base + 7 * stride];
+    storeCellS(cellMem, c);
 }
-ESB_DEV void storeCell(const Cell &c, double *S, size_t stride, size_t base) {
+ESB_DEV void storeCell(const double *cellMem, double *S, size_t stride, size_t base) {
+    const Cell c = loadCellS(cellMem);
     S[base] = c.n; S[base + stride] = c.E; S[base + 2 * stride] = c.V; S[base + 3 * stride] = c.mx;
     S[base + 4 * stride] = c.my; S[base + 5 * stride] = c.pf; S[base + 6 * stride] = c.pi; S[base + 7 * stride] = c.po;
 }
@@ -56,7 +109,7 @@ ESB_DEV double scheduleValue(const long long *keyStep, const double *keyVal, int
 }
 
 template <int G>
-ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &g) {
+ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &g, const GasView &v) {
     const EsbDeviceParams *D = a.D;
     const size_t n = (size_t)a.nInst;
     double *S = a.S;
@@ -79,14 +132,18 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &
     s.clutchTorque = S[(size_t)ESB_GF_CLUTCH_TORQUE * n + inst];
     s.lastIter = (int)S[(size_t)ESB_GF_LAST_ITER * n + inst];
     s.totalExhaustFlow = S[(size_t)ESB_GF_TOTAL_EXH_FLOW * n + inst];
-    loadCell(s.plenum, S, n, (size_t)(ESB_GF_PLENUM + 8 * k.shIn) * n + inst);
-    loadCell(s.collector, S, n, (size_t)(ESB_GF_COLLECTOR + 8 * k.shEx) * n + inst);
+    // gas cells into shared memory: lane c brings its cylinder's three, the plenums and collectors are dealt out over the lanes
+    for (int i = g.lane; i < k.nIn; i += G) loadCell(plenumPtr(v, k.N, i), S, n, (size_t)(ESB_GF_PLENUM + 8 * i) * n + inst);
+    for (int e = g.lane; e < D->P.exhaustSystemCount; e += G) loadCell(collectorPtr(v, k.N, k.nIn, e), S, n, (size_t)(ESB_GF_COLLECTOR + 8 * e) * n + inst);
     loadBody(s.piston, S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_PISTON, cyl) * n + inst);
     loadBody(s.rod, S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_ROD, cyl) * n + inst);
     for (int r = 0; r < 5; ++r) s.lam[r] = S[(size_t)ESB_CYL_FIELD(ESB_CF_LAMBDA + r, cyl) * n + inst];
-    loadCell(s.chamber, S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_CHAMBER, cyl) * n + inst);
-    loadCell(s.intr, S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_INTAKE_RUNNER, cyl) * n + inst);
-    loadCell(s.exhr, S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_EXHAUST_RUNNER, cyl) * n + inst);
+    if (k.active) {
+        loadCell(chamberPtr(v, cyl), S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_CHAMBER, cyl) * n + inst);
+        loadCell(intakeRunnerPtr(v, cyl), S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_INTAKE_RUNNER, cyl) * n + inst);
+        loadCell(exhaustRunnerPtr(v, cyl), S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_EXHAUST_RUNNER, cyl) * n + inst);
+    }
+    g.slotSync();
     s.flameLit = S[(size_t)ESB_CYL_FIELD(ESB_CF_FLAME + 0, cyl) * n + inst];
     s.flameTX = S[(size_t)ESB_CYL_FIELD(ESB_CF_FLAME + 1, cyl) * n + inst];
     s.flameTY = S[(size_t)ESB_CYL_FIELD(ESB_CF_FLAME + 2, cyl) * n + inst];
@@ -123,7 +180,7 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &
         double out[ESB_MAX_EXHAUST];
         // exhaust-flow total: on telemetry steps, and on the last step of every launch so that the stored statistic
         // (EsbBatchGetStats().exhaustFlow, BridgeSimulator::getStats) is current whatever the telemetry interval
-        const double exhaustFlow = simulateStep<G>(s, k, D, ctl, g, seed, delayed, out, sample || step + 1 == a.nSteps);
+        const double exhaustFlow = simulateStep<G>(s, k, D, ctl, g, v, seed, delayed, out, sample || step + 1 == a.nSteps);
         if (k.active) {
             if (live) ring[(size_t)s.delayPos * ringStride] = exhaustFlow;
             s.delayPos = (s.delayPos + 1 == k.delayLen) ? 0 : s.delayPos + 1;
@@ -132,9 +189,9 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &
             for (int c = 0; c < a.channels; ++c) a.stream[((size_t)step * a.channels + c) * n + inst] = out[c];
         }
         if (sample) {
-            const double p0 = g.bcast(cellPressure(s.chamber), 0);
-            const double pMan = g.bcast(cellPressure(s.plenum), k.plen0Lane);
             if (g.lane == 0 && live) {
+                const double p0 = cellPressure(loadCellS(chamberPtr(v, 0)));
+                const double pMan = cellPressure(loadCellS(plenumPtr(v, k.N, 0)));
                 const long long idx = (gstep + 1) / a.telemetryEvery - 1 - a.telemetryBase;
                 double *t = a.telemetry + (size_t)idx * ESB_TELEMETRY_STRIDE * n + inst;
                 t[0 * n] = -s.crank.w * (30.0 / kPi);
@@ -166,27 +223,15 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &
         S[(size_t)ESB_GF_LAST_ITER * n + inst] = (double)s.lastIter;
         S[(size_t)ESB_GF_TOTAL_EXH_FLOW * n + inst] = s.totalExhaustFlow;
     }
-    if (k.chainMode) {
-        if (k.roleP && !k.helper) storeCell(s.plenum, S, n, (size_t)(ESB_GF_PLENUM + 8 * k.shIn) * n + inst);
-        if (k.roleC && !k.helper) storeCell(s.collector, S, n, (size_t)(ESB_GF_COLLECTOR + 8 * k.shEx) * n + inst);
-    } else if (k.active) {
-        // the first cylinder plumbed to an intake / exhaust system stores that replica
-        const EsbEngineParams &P = D->P;
-        bool firstIn = true, firstEx = true;
-        for (int t = 0; t < g.lane; ++t) {
-            if (P.cyl[t].intake == k.inIdx) firstIn = false;
-            if (P.cyl[t].exhaustSystem == k.exIdx) firstEx = false;
-        }
-        if (firstIn) storeCell(s.plenum, S, n, (size_t)(ESB_GF_PLENUM + 8 * k.inIdx) * n + inst);
-        if (firstEx) storeCell(s.collector, S, n, (size_t)(ESB_GF_COLLECTOR + 8 * k.exIdx) * n + inst);
-    }
+    for (int i = g.lane; i < k.nIn; i += G) storeCell(plenumPtr(v, k.N, i), S, n, (size_t)(ESB_GF_PLENUM + 8 * i) * n + inst);
+    for (int e = g.lane; e < D->P.exhaustSystemCount; e += G) storeCell(collectorPtr(v, k.N, k.nIn, e), S, n, (size_t)(ESB_GF_COLLECTOR + 8 * e) * n + inst);
     if (k.active) {
         storeBody(s.piston, S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_PISTON, cyl) * n + inst);
         storeBody(s.rod, S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_ROD, cyl) * n + inst);
         for (int r = 0; r < 5; ++r) S[(size_t)ESB_CYL_FIELD(ESB_CF_LAMBDA + r, cyl) * n + inst] = s.lam[r];
-        storeCell(s.chamber, S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_CHAMBER, cyl) * n + inst);
-        storeCell(s.intr, S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_INTAKE_RUNNER, cyl) * n + inst);
-        storeCell(s.exhr, S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_EXHAUST_RUNNER, cyl) * n + inst);
+        storeCell(chamberPtr(v, cyl), S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_CHAMBER, cyl) * n + inst);
+        storeCell(intakeRunnerPtr(v, cyl), S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_INTAKE_RUNNER, cyl) * n + inst);
+        storeCell(exhaustRunnerPtr(v, cyl), S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_EXHAUST_RUNNER, cyl) * n + inst);
         S[(size_t)ESB_CYL_FIELD(ESB_CF_FLAME + 0, cyl) * n + inst] = s.flameLit;
         S[(size_t)ESB_CYL_FIELD(ESB_CF_FLAME + 1, cyl) * n + inst] = s.flameTX;
         S[(size_t)ESB_CYL_FIELD(ESB_CF_FLAME + 2, cyl) * n + inst] = s.flameTY;

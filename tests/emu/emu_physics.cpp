@@ -25,11 +25,18 @@ double *emuSlots(EmuShared *s) { return s->slots; }
 
 template <int G> static void runGroup(const esbk::RunArgs &a, int inst) {
     esbk::EmuShared sh(G);
+    // the block's "shared memory": same layout as on the device, one lane group
+    const EsbGasNet &gn = a.D->gas;
+    const esbk::GasSmemLayout L = esbk::gasSmemLayout(gn, a.D->P.cylinderCount, a.D->P.intakeCount, a.D->fluidSteps, 1);
+    std::vector<double> mem(L.total / sizeof(double) + 2, 0.0);
+    unsigned char *base = reinterpret_cast<unsigned char *>(mem.data());
+    esbk::gasTablesToShared(base, L, gn, 0, 1);
+    const esbk::GasView view = esbk::gasViewAt(base, L, gn, 0);
     std::vector<std::thread> th;
     for (int lane = 0; lane < G; ++lane)
         th.emplace_back([&, lane] {
             esbk::Group<G> g; g.lane = lane; g.mask = 0; g.sh = &sh;
-            esbk::runInstance<G>(a, inst, true, g);
+            esbk::runInstance<G>(a, inst, true, g, view);
         });
     for (auto &t : th) t.join();
 }
@@ -48,6 +55,7 @@ int emu_physics_run(const EsbEngineParams *P, double simFreq, int fluidSteps, in
     a.nKeys = nKeys; a.keyStep = keyStep; a.keyThrottle = keyThrottle; a.keyDynoSpeed = keyDyno;
     a.stream = stream; a.channels = P->exhaustSystemCount; a.telemetry = telemetry; a.telemetryEvery = telemetryEvery; a.telemetryBase = stepBase / (telemetryEvery > 0 ? telemetryEvery : 1);
     const int G = lanesOverride > 0 ? lanesOverride : D.lanesPerInstance;
+    if (G != D.lanesPerInstance) { D.lanesPerInstance = G; esb::buildGasNet(*P, D); }   // the slot schedule is built for the lane count
     for (int inst = 0; inst < nInst; ++inst) {
         switch (G) {
         case 1: runGroup<1>(a, inst); break;

@@ -16,7 +16,7 @@ _lib = None
 def build():
     csrc = os.path.join(ROOT, "engine-sim-cli_b200", "csrc")
     out = os.path.join(HERE, "emu", "libemu_physics.so")
-    srcs = [os.path.join(HERE, "emu", "emu_physics.cpp"), os.path.join(csrc, "instance_init.cpp")]
+    srcs = [os.path.join(HERE, "emu", "emu_physics.cpp"), os.path.join(csrc, "instance_init.cpp"), os.path.join(csrc, "gas_schedule.cpp")]
     deps = srcs + [os.path.join(csrc, f) for f in ("physics_core.cuh", "physics_run.cuh", "esb_device.h", "host.h")] + \
         [os.path.join(ROOT, "include", f) for f in ("esb_math.h", "esb_params.h")]
     if os.path.exists(out) and all(os.path.getmtime(out) >= os.path.getmtime(d) for d in deps):

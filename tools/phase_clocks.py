@@ -15,8 +15,8 @@ import bench
 import engine_sim_cli_b200 as esb
 from engine_sim_cli_b200 import api
 
-NAMES = ["prelude", "solver", "ignition+chamber+valveK", "slotA(inlet/outlet)", "slotB(relax shared)", "blowby", "chain slots", "valve slots",
-         "runner relax", "tail+audio", "chain: bcast in", "chain: barrier", "chain: exchange call", "chain: bcast out", "", ""]
+NAMES = ["prelude", "solver", "ignition+chamber+valveK", "gas schedule (unattributed)", "slot barrier", "exchange slot", "relax slot", "",
+         "", "totals+audio", "slot table read", "", "", "", "", ""]
 
 
 def run(n, steps=300, settle=1500):
