@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(256, (MINB >= 7 ? 2 : 1)) esb_physics_kernel(R
     extern __shared__ __align__(16) unsigned char esbSmem[];
     const EsbGasNet &gn = a.D->gas;
     const GasSmemLayout L = gasSmemLayout(gn, a.D->P.cylinderCount, a.D->P.intakeCount, a.D->fluidSteps, blockDim.x / G);
-    gasTablesToShared(esbSmem, L, gn, threadIdx.x, blockDim.x);
+    gasTablesToShared(esbSmem, L, a.D, threadIdx.x, blockDim.x);
     __syncthreads();
     const GasView view = gasViewAt(esbSmem, L, gn, threadIdx.x / G);
     Group<G> g;

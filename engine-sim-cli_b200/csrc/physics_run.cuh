@@ -29,7 +29,7 @@ struct RunArgs {
 
 // Shared-memory carve-up of one block: the gas-network tables (one copy per block), then one region per lane group
 // (instance) with its cells, its per-step flow constants and its exhaust-valve flow record.  Offsets in bytes, 16-byte aligned.
-struct GasSmemLayout { unsigned offType, offOps, offExchange, offRelax, offConst, offInst, instBytes, kStepDoubles, total; };
+struct GasSmemLayout { unsigned offType, offOps, offExchange, offRelax, offGasConst, offConst, offInst, instBytes, kStepDoubles, total; };
 #if defined(__CUDACC__)
 __host__ __device__
 #endif
@@ -40,7 +40,8 @@ inline GasSmemLayout gasSmemLayout(const EsbGasNet &gn, int nCyl, int nIntakes, 
     L.offOps = up((unsigned)gn.nSlots);
     L.offExchange = L.offOps + up((unsigned)(gn.nSlots * gn.entriesPerSlot * sizeof(uint16_t)));
     L.offRelax = L.offExchange + up((unsigned)((gn.nExchange + 1) * sizeof(EsbGasExchange)));
-    L.offConst = L.offRelax + up((unsigned)(gn.nRelax * sizeof(EsbGasRelax)));
+    L.offGasConst = L.offRelax + up((unsigned)(gn.nRelax * sizeof(EsbGasRelax)));
+    L.offConst = L.offGasConst + up((unsigned)sizeof(GasConst));
     L.offInst = L.offConst + up((unsigned)(gn.nConst * ESB_GAS_CELL_STRIDE * sizeof(double)));
     L.kStepDoubles = (unsigned)((2 * nCyl + nIntakes + 1) & ~1);
     L.instBytes = up((unsigned)((gn.nCells * ESB_GAS_CELL_STRIDE + L.kStepDoubles + fluidSteps * nCyl) * sizeof(double))) + 16u;   // +16: neighbours start one bank group apart
@@ -55,6 +56,7 @@ ESB_DEV GasView gasViewAt(unsigned char *base, const GasSmemLayout &L, const Esb
     v.exchange = reinterpret_cast<const EsbGasExchange *>(base + L.offExchange);
     v.relax = reinterpret_cast<const EsbGasRelax *>(base + L.offRelax);
     v.constCells = reinterpret_cast<const double *>(base + L.offConst);
+    v.gc = reinterpret_cast<const GasConst *>(base + L.offGasConst);
     v.cells = reinterpret_cast<double *>(base + L.offInst + (size_t)L.instBytes * group);
     v.kStep = v.cells + gn.nCells * ESB_GAS_CELL_STRIDE;
     v.flows = v.kStep + L.kStepDoubles;
@@ -62,7 +64,9 @@ ESB_DEV GasView gasViewAt(unsigned char *base, const GasSmemLayout &L, const Esb
     return v;
 }
 // Copies the tables into the block's shared memory: element i of each table by thread (tid + k * nThreads).
-ESB_DEV void gasTablesToShared(unsigned char *base, const GasSmemLayout &L, const EsbGasNet &gn, int tid, int nThreads) {
+ESB_DEV void gasTablesToShared(unsigned char *base, const GasSmemLayout &L, const EsbDeviceParams *D, int tid, int nThreads) {
+    const EsbGasNet &gn = D->gas;
+    if (tid == 0) *reinterpret_cast<GasConst *>(base + L.offGasConst) = makeGasConst(D->hcr, D->chokedFlowLimit, D->chokedFlowFactor);
     for (int i = tid; i < gn.nSlots; i += nThreads) base[L.offType + i] = gn.slotType[i];
     uint16_t *ops = reinterpret_cast<uint16_t *>(base + L.offOps);
     for (int i = tid; i < gn.nSlots * gn.entriesPerSlot; i += nThreads) ops[i] = gn.slotOps[(i / gn.entriesPerSlot) * 16 + (i % gn.entriesPerSlot)];
@@ -115,8 +119,7 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &
     double *S = a.S;
     LaneConst k;
     loadLaneConst<G>(k, D, g.lane);
-    GasConst gcMem = k.gc;
-    k.gcp = &gcMem;
+    k.gcp = v.gc;
     const int cyl = k.active ? g.lane : 0;
     LaneState s;
     loadBody(s.crank, S, n, (size_t)ESB_GF_CRANK * n + inst);

@@ -30,7 +30,7 @@ template <int G> static void runGroup(const esbk::RunArgs &a, int inst) {
     const esbk::GasSmemLayout L = esbk::gasSmemLayout(gn, a.D->P.cylinderCount, a.D->P.intakeCount, a.D->fluidSteps, 1);
     std::vector<double> mem(L.total / sizeof(double) + 2, 0.0);
     unsigned char *base = reinterpret_cast<unsigned char *>(mem.data());
-    esbk::gasTablesToShared(base, L, gn, 0, 1);
+    esbk::gasTablesToShared(base, L, a.D, 0, 1);
     const esbk::GasView view = esbk::gasViewAt(base, L, gn, 0);
     std::vector<std::thread> th;
     for (int lane = 0; lane < G; ++lane)
