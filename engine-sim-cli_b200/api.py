@@ -7,7 +7,6 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 ESIM_SUCCESS = 0
 TELEMETRY_STRIDE = 8
-PARAMS_SIZE = 105816
 
 _lib = None
 
@@ -43,6 +42,25 @@ class EngineSimStats(C.Structure):
 
 
 Controls = EsbControls
+_layout = None
+
+
+def _get_layout():
+    """(sizeof(EsbEngineParams), state fields) of the loaded library build."""
+    global _layout
+    if _layout is None:
+        a, b = C.c_int32(), C.c_int32()
+        lib().EsbGetLayout(C.byref(a), C.byref(b))
+        _layout = (a.value, b.value)
+    return _layout
+
+
+def params_size():
+    return _get_layout()[0]
+
+
+def state_fields():
+    return _get_layout()[1]
 
 
 def lib():
@@ -66,7 +84,7 @@ def lib():
             "EsbBatchGetLastStream": [vp, vp, i32, C.POINTER(i32)], "EsbBatchGetStats": [vp, i32, vp], "EsbBatchWriteWavs": [vp, C.c_char_p, C.c_char_p],
             "EsbBatchSetLaunchConfig": [vp, i32, i32], "EsbBatchGetLaunchCounts": [vp, vp],
             "EsbBatchSetProfiling": [vp, i32], "EsbBatchSetPhysicsShape": [vp, i32, i32], "EsbBatchGetKernelTimes": [vp, vp, vp],
-            "EsbFirRun": [vp, i64, i64, vp, i32, i32, i32, i32, i64, vp, i64, vp], "EsbProbePeak": [i32, i32, C.POINTER(dbl)],
+            "EsbFirRun": [vp, i64, i64, vp, i32, i32, i32, i32, i64, vp, i64, vp], "EsbProbePeak": [i32, i32, C.POINTER(dbl)], "EsbGetLayout": [C.POINTER(i32), C.POINTER(i32)],
             "EsbCheckFastArith": [i32, i32, vp, vp, vp, vp],
             "EngineSimCreate": [vp, C.POINTER(vp)], "EngineSimLoadScript": [vp, C.c_char_p, C.c_char_p], "EngineSimLoadParams": [vp, vp, vp, i32, flt],
             "EngineSimDestroy": [vp], "EngineSimSetThrottle": [vp, dbl], "EngineSimSetSpeedControl": [vp, dbl], "EngineSimSetIgnition": [vp, i32],
@@ -93,7 +111,6 @@ def _ptr(a):
 
 
 # esb_device.h: ESB_GF_COUNT + ESB_CF_COUNT * ESB_MAX_CYL
-STATE_FIELDS = (28 + 8 * 4 + 8 * 4) + (49 + 32) * 16
 
 
 class BatchSimulator:
@@ -133,8 +150,8 @@ class BatchSimulator:
 
     # ---- loading ----
     def load_params(self, blob: bytes):
-        if len(blob) != PARAMS_SIZE:
-            raise EngineSimError(-4, f"parameter blob has {len(blob)} bytes, expected {PARAMS_SIZE}")
+        if len(blob) != params_size():
+            raise EngineSimError(-4, f"parameter blob has {len(blob)} bytes, expected {params_size()}")
         buf = C.create_string_buffer(blob, len(blob))
         self._check(lib().EsbBatchLoadParams(self.h, buf))
         self.channels = int(np.frombuffer(blob[:16], dtype=np.int32)[2])
@@ -252,10 +269,10 @@ class BatchSimulator:
         return ptr.value, stride.value, n.value
 
     def state(self):
-        S = np.zeros((STATE_FIELDS, self.n))
+        S = np.zeros((state_fields(), self.n))
         f = C.c_int32()
         self._check(lib().EsbBatchGetState(self.h, _ptr(S), C.byref(f)))
-        assert f.value == STATE_FIELDS
+        assert f.value == state_fields()
         return S
 
     def last_stream(self, max_steps):

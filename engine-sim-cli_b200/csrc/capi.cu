@@ -212,6 +212,11 @@ int32_t EsbCheckFastArith(int32_t op, int32_t n, const double *a, const double *
     return ok ? ESIM_SUCCESS : ESIM_ERROR_CUDA;
 }
 
+int32_t EsbGetLayout(int32_t *outParamsBytes, int32_t *outStateFields) {
+    if (outParamsBytes) *outParamsBytes = (int32_t)sizeof(EsbEngineParams);
+    if (outStateFields) *outStateFields = ESB_STATE_FIELDS;
+    return ESIM_SUCCESS;
+}
 int32_t EsbProbePeak(int32_t fp64, int32_t fma, double *outGflops) {
     if (!outGflops) return ESIM_ERROR_INVALID_PARAMETER;
     int dev = 0, sms = 0;

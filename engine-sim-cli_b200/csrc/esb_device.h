@@ -31,6 +31,8 @@ enum EsbGlobalField {
     ESB_GF_CLUTCH_TORQUE,
     ESB_GF_LAST_ITER,
     ESB_GF_TOTAL_EXH_FLOW,
+    ESB_GF_EXACT_OPS,                          /* diagnostic: gas operations of this instance that left the straight-line arithmetic
+                                                  (an operand outside its exact range) and were redone with plain IEEE / and sqrt */
     ESB_GF_PLENUM,                             /* ESB_MAX_INTAKE x cell(8) */
     ESB_GF_COLLECTOR = ESB_GF_PLENUM + 8 * ESB_MAX_INTAKE, /* ESB_MAX_EXHAUST x cell(8) */
     ESB_GF_COUNT = ESB_GF_COLLECTOR + 8 * ESB_MAX_EXHAUST
@@ -74,7 +76,9 @@ enum EsbCtlField {
  * per-step code, so hoisting them changes no bit of the result). */
 typedef struct EsbCylDerived {
     double sinBank, cosBank;       /* esb_sincos(bankAngle) */
-    double journalLX, journalLY;   /* crankThrow * cos/sin(journalAngle) */
+    double journalLX, journalLY;   /* the rod's journal in the coordinates of the body that carries it: crankThrow * cos/sin(journalAngle)
+                                      on the crankshaft, (-sin(a), bigEnd + cos(a)) * slaveThrow on a master rod (a = slaveJournalAngle) */
+    double parentInvMass, parentInvInertia; /* of that body (crankshaft, or the master rod) */
     double littleEnd, bigEnd;      /* rod attachment points in rod coordinates */
     double boreArea;               /* pi * (bore/2)^2 */
     double invPistonMass, invRodMass, invRodInertia;

@@ -90,6 +90,14 @@ void deriveDeviceParams(const EsbEngineParams &P, double simFreq, int fluidSteps
         esb_sincos(c.bankAngle, &d.sinBank, &d.cosBank);
         double sJ, cJ; esb_sincos(P.journalAngle[c.journal], &sJ, &cJ);
         d.journalLX = P.crankThrow * cJ; d.journalLY = P.crankThrow * sJ;
+        d.parentInvMass = D.invCrankMass; d.parentInvInertia = D.invCrankInertia;
+        if (c.masterCylinder >= 0) {   // slave rod: the journal is a point of the master rod (oracle/solver.cpp, same expressions)
+            const EsbCylinder &mc = P.cyl[c.masterCylinder];
+            double sA, cA; esb_sincos(c.slaveJournalAngle, &sA, &cA);
+            const double masterBigEnd = -(0.5 * mc.rodLength + mc.rodCenterOfMass);
+            d.journalLX = -sA * mc.slaveThrow; d.journalLY = masterBigEnd + cA * mc.slaveThrow;
+            d.parentInvMass = 1.0 / mc.rodMass; d.parentInvInertia = 1.0 / mc.rodMomentOfInertia;
+        }
         d.littleEnd = 0.5 * c.rodLength - c.rodCenterOfMass;
         d.bigEnd = -(0.5 * c.rodLength + c.rodCenterOfMass);
         d.boreArea = kPi * (0.5 * c.bore) * (0.5 * c.bore);
@@ -123,7 +131,16 @@ void initialStateColumn(const EsbDeviceParams &D, std::vector<double> &col) {
     for (int i = 0; i < N; ++i) {
         const EsbCylinder &c = P.cyl[i];
         const double phi = P.journalAngle[c.journal];
-        const double jx = P.crankPosX + P.crankThrow * esb_cos(phi), jy = P.crankPosY + P.crankThrow * esb_sin(phi);
+        double jx = P.crankPosX + P.crankThrow * esb_cos(phi), jy = P.crankPosY + P.crankThrow * esb_sin(phi);
+        if (c.masterCylinder >= 0) {   // slave rod (radial engines): the journal is a point of the master rod, which is already placed
+            const EsbCylinder &mc = P.cyl[c.masterCylinder];
+            const int mf = ESB_CYL_FIELD(ESB_CF_ROD, c.masterCylinder);
+            const double mpx = col[mf], mpy = col[mf + ESB_MAX_CYL], mth = col[mf + 2 * ESB_MAX_CYL];
+            const double lx = -esb_sin(c.slaveJournalAngle) * mc.slaveThrow;
+            const double ly = -(0.5 * mc.rodLength + mc.rodCenterOfMass) + esb_cos(c.slaveJournalAngle) * mc.slaveThrow;
+            const double sM = esb_sin(mth), cM = esb_cos(mth);
+            jx = mpx + (cM * lx - sM * ly); jy = mpy + (sM * lx + cM * ly);
+        }
         const double dx = -esb_sin(c.bankAngle), dy = esb_cos(c.bankAngle);
         const double nx = dy, ny = -dx;
         const double rx = jx - c.bankX, ry = jy - c.bankY;

@@ -29,7 +29,7 @@ struct RunArgs {
 
 // Shared-memory carve-up of one block: the gas-network tables (one copy per block), then one region per lane group
 // (instance) with its cells, its per-step flow constants and its exhaust-valve flow record.  Offsets in bytes, 16-byte aligned.
-struct GasSmemLayout { unsigned offType, offOps, offExchange, offRelax, offGasConst, offConst, offInst, instBytes, kStepDoubles, total; };
+struct GasSmemLayout { unsigned offType, offOps, offExchange, offRelax, offGasConst, offConst, offInst, instBytes, kStepDoubles, flowDoubles, total; };
 #if defined(__CUDACC__)
 __host__ __device__
 #endif
@@ -44,7 +44,8 @@ inline GasSmemLayout gasSmemLayout(const EsbGasNet &gn, int nCyl, int nIntakes, 
     L.offConst = L.offGasConst + up((unsigned)sizeof(GasConst));
     L.offInst = L.offConst + up((unsigned)(gn.nConst * ESB_GAS_CELL_STRIDE * sizeof(double)));
     L.kStepDoubles = (unsigned)((2 * nCyl + nIntakes + 1) & ~1);
-    L.instBytes = up((unsigned)((gn.nCells * ESB_GAS_CELL_STRIDE + L.kStepDoubles + fluidSteps * nCyl) * sizeof(double))) + 16u;   // +16: neighbours start one bank group apart
+    L.flowDoubles = (unsigned)(fluidSteps * nCyl);
+    L.instBytes = up((unsigned)((gn.nCells * ESB_GAS_CELL_STRIDE + L.kStepDoubles + L.flowDoubles + 1) * sizeof(double))) + 16u;   // +16: neighbours start one bank group apart
     L.total = L.offInst + L.instBytes * (unsigned)groups;
     return L;
 }
@@ -60,6 +61,7 @@ ESB_DEV GasView gasViewAt(unsigned char *base, const GasSmemLayout &L, const Esb
     v.cells = reinterpret_cast<double *>(base + L.offInst + (size_t)L.instBytes * group);
     v.kStep = v.cells + gn.nCells * ESB_GAS_CELL_STRIDE;
     v.flows = v.kStep + L.kStepDoubles;
+    v.exactOps = v.flows + L.flowDoubles;
     v.nSlots = gn.nSlots; v.entries = gn.entriesPerSlot; v.nCells = gn.nCells; v.nExchange = gn.nExchange;
     return v;
 }
@@ -146,6 +148,7 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &
         loadCell(intakeRunnerPtr(v, cyl), S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_INTAKE_RUNNER, cyl) * n + inst);
         loadCell(exhaustRunnerPtr(v, cyl), S, n * ESB_MAX_CYL, (size_t)ESB_CYL_FIELD(ESB_CF_EXHAUST_RUNNER, cyl) * n + inst);
     }
+    if (g.lane == 0) *v.exactOps = 0.0;
     g.slotSync();
     s.flameLit = S[(size_t)ESB_CYL_FIELD(ESB_CF_FLAME + 0, cyl) * n + inst];
     s.flameTX = S[(size_t)ESB_CYL_FIELD(ESB_CF_FLAME + 1, cyl) * n + inst];
@@ -225,6 +228,7 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &
         S[(size_t)ESB_GF_CLUTCH_TORQUE * n + inst] = s.clutchTorque;
         S[(size_t)ESB_GF_LAST_ITER * n + inst] = (double)s.lastIter;
         S[(size_t)ESB_GF_TOTAL_EXH_FLOW * n + inst] = s.totalExhaustFlow;
+        S[(size_t)ESB_GF_EXACT_OPS * n + inst] += *v.exactOps;
     }
     for (int i = g.lane; i < k.nIn; i += G) storeCell(plenumPtr(v, k.N, i), S, n, (size_t)(ESB_GF_PLENUM + 8 * i) * n + inst);
     for (int e = g.lane; e < D->P.exhaustSystemCount; e += G) storeCell(collectorPtr(v, k.N, k.nIn, e), S, n, (size_t)(ESB_GF_COLLECTOR + 8 * e) * n + inst);

@@ -184,8 +184,15 @@ void parsePreset(const std::string &text, LoadedPreset &out) {
             d.rodMomentOfInertia = r.number("momentOfInertia", rc);
             d.rodCenterOfMass = r.number("centerOfMass", rc);
             d.rodLength = r.number("length", rc);
-            if (r.numberOr("slaveThrow", 0.0) != 0.0) throw JsonError("Master/slave rods (slaveThrow != 0) are not supported yet in " + rc);
+            d.slaveThrow = r.numberOr("slaveThrow", 0.0);
+            // The reference's schema has no master link (PresetSerializer.cpp:59-67 writes "journal" and "slaveThrow" only);
+            // presets compiled by this repo's script front-end add "masterCylinder" / "slaveJournalAngle" to the rod.
+            d.masterCylinder = (int)r.numberOr("masterCylinder", -1.0);
+            d.slaveJournalAngle = r.numberOr("slaveJournalAngle", 0.0);
+            if (d.masterCylinder >= g) throw JsonError("masterCylinder must name an earlier cylinder in " + rc);
+            if (d.masterCylinder >= 0 && p.cyl[d.masterCylinder].masterCylinder >= 0) throw JsonError("a slave rod cannot be a master in " + rc);
             d.journal = c.has("rodJournalIndex") ? (int)c.number("rodJournalIndex", cc) : g;
+            if (d.masterCylinder >= 0) d.journal = 0;
             if (d.journal < 0 || d.journal >= p.journalCount) throw JsonError("rodJournalIndex out of range in " + cc);
             d.combustionChamberVolume = head.number("combustionChamberVolume", hc);
             d.intakeRunnerVolume = head.number("intakeRunnerVolume", hc);

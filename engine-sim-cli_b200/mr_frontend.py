@@ -753,23 +753,38 @@ def to_preset(interp, source_script=""):
     exhausts, intakes = [], []
     banks_json, chambers, firing = [], [], []
     posts = e["ignition"]["posts"] if e["ignition"] else []
+    # master / slave rods (radial engines): a slave rod's journal was added to a ROD (add_slave_journal) instead of a crankshaft;
+    # the preset then names the cylinder whose rod carries it ("masterCylinder", global cylinder index) and the journal's angle.
+    rod_owner, g_index = {}, 0
+    for b in e["banks"]:
+        for c in b["cylinders"]:
+            rod_owner.setdefault(id(c["rod"]), g_index)
+            g_index += 1
+    g_index = 0
     for bi, b in enumerate(e["banks"]):
         if b["head"] is None:
             raise MrError(f"cylinder bank {bi} has no cylinder head")
         cyls, head_cyls = [], []
         for ci, c in enumerate(b["cylinders"]):
             rod, j = c["rod"], c["journal"]
-            if rod.get("slaveJournals") or j.get("masterRod") is not None:
-                raise MrError("master / slave connecting rods (radial engines) are not supported by the batched physics")
-            crank = j["crank"]
-            if crank is None:
-                raise MrError("a cylinder uses a rod journal that was never added to a crankshaft")
-            ji = _index_of(list(crank["rodJournals"]), j)
+            master_cyl, slave_angle = -1, 0.0
+            if j.get("masterRod") is not None:
+                master_cyl = rod_owner.get(id(j["masterRod"]), -1)
+                if master_cyl < 0 or master_cyl >= g_index:
+                    raise MrError("a slave rod's master rod must belong to an earlier cylinder")
+                slave_angle, ji = j["angle"], 0
+            else:
+                crank = j["crank"]
+                if crank is None:
+                    raise MrError("a cylinder uses a rod journal that was never added to a crankshaft")
+                ji = _index_of(list(crank["rodJournals"]), j)
+            g_index += 1
             cyls.append({"pistonMass": c["piston"]["pistonMass"], "compressionHeight": c["piston"]["compressionHeight"],
                          "wristPinPosition": c["piston"]["wristPinPosition"], "displacement": c["piston"]["displacement"], "blowbyK": c["piston"]["blowbyK"],
                          "cylinderIndex": ci,
                          "connectingRod": {"mass": rod["mass"], "momentOfInertia": rod["momentOfInertia"], "centerOfMass": rod["centerOfMass"],
-                                           "length": rod["length"], "journal": ji, "slaveThrow": rod["slaveThrow"]},
+                                           "length": rod["length"], "journal": ji, "slaveThrow": rod["slaveThrow"],
+                                           "masterCylinder": master_cyl, "slaveJournalAngle": slave_angle},
                          "rodJournalIndex": ji, "rodJournalCount": 0,
                          "exhaustSystemIndex": _index_of(exhausts, c["exhaust"]), "intakeIndex": _index_of(intakes, c["intake"])})
             head_cyls.append({"soundAttenuation": c["soundAttenuation"], "headerPrimaryLength": c["primaryLength"]})

@@ -179,6 +179,9 @@ int32_t EsbFirRun(const float *dX, int64_t xStride, int64_t hist, const float *d
                   int32_t rows, int64_t count, float *dY, int64_t yStride, void *cudaStream);
 /* Pipe peak probes: runs a register-resident loop and returns achieved GFLOP/s (fp64: 0/1, fma: 0/1). */
 int32_t EsbProbePeak(int32_t fp64, int32_t fma, double *outGflops);
+/* Sizes of the binary contracts of this build: sizeof(EsbEngineParams) (the parameter blob of EsbBatchLoadParams /
+ * EngineSimLoadParams) and the number of fields of the state block EsbBatchGetState returns. */
+int32_t EsbGetLayout(int32_t *outParamsBytes, int32_t *outStateFields);
 /* Self-check of the physics kernel's branch-free division (op 0: out = a / b) and square root (op 1: out = sqrt(a)):
  * HOST arrays of n doubles; flagged[i] = 1 where the kernel would fall back to the plain IEEE operation instead. */
 int32_t EsbCheckFastArith(int32_t op, int32_t n, const double *a, const double *b, double *out, uint32_t *flagged);

@@ -46,8 +46,14 @@ typedef struct EsbCylinder {
     double pistonMass, compressionHeight, wristPinPosition, blowbyK;
     /* connecting rod (ConnectingRodDeserializer.cpp) */
     double rodMass, rodMomentOfInertia, rodCenterOfMass, rodLength;
-    int32_t journal; /* rod journal on crankshaft 0 */
-    int32_t pad0;
+    int32_t journal; /* rod journal on crankshaft 0 (a rod on the crankshaft) */
+    /* master / slave rods of radial engines (es/engines/atg-video-2/09_radial_9.mr:145-165; ConnectingRod "slaveThrow",
+     * PresetSerializer.cpp:65): a slave rod's big end rides on a journal of its master rod instead of the crankshaft.
+     * masterCylinder = -1 for a rod on the crankshaft, else the cylinder whose rod carries this rod's journal (it must
+     * come earlier in cylinder order); slaveJournalAngle is that journal's angle on the master (same convention as a
+     * bank angle: from the master rod's own axis, counter-clockwise), at radius slaveThrow OF THE MASTER from its big end. */
+    int32_t masterCylinder;
+    double slaveThrow, slaveJournalAngle;
     /* head (CylinderHeadDeserializer.cpp:126-154) */
     double combustionChamberVolume;
     double intakeRunnerVolume, intakeRunnerCrossSectionArea;

@@ -12,6 +12,28 @@ static double positiveMod(double x, double m) {
     return (r < 0) ? r + m : r;
 }
 
+// How complete a burn can get, 0..1 -> [lowEfficiencyAttenuation, 1].  The three parameters are required by the
+// reference's fuel schema and handed to Fuel::initialize (src/preset/FuelDeserializer.cpp:26-39; defaults 0.6 / 2.0 / 10.0 in
+// es/objects/objects.mr:59-63); the body that consumes them is in the absent submodule.  Restated from their names,
+// ranges and defaults (ASSUMPTIONS.md #7): turbulence (the mean-piston-speed function's output) saturates its benefit at
+// maxTurbulenceEffect; dilution = inert gas in the charge relative to the inert gas its oxygen arrived with as air
+// (1 = no residuals), harmful up to maxDilutionEffect.
+static double burnQuality(double turbulence, double p_inert, double p_o2, double lowAttenuation, double maxTurbulence, double maxDilution) {
+    double t = (maxTurbulence > 0) ? turbulence / maxTurbulence : 1.0;
+    if (t < 0) t = 0;
+    if (t > 1) t = 1;
+    const double inertFresh = (0.79 / 0.21) * p_o2;
+    double d = 0;
+    if (maxDilution > 1.0) {
+        const double dilution = (inertFresh > 0) ? p_inert / inertFresh : maxDilution;
+        d = (dilution - 1.0) / (maxDilution - 1.0);
+        if (d < 0) d = 0;
+        if (d > 1) d = 1;
+    }
+    const double quality = t * (1.0 - d);
+    return lowAttenuation + (1.0 - lowAttenuation) * quality;
+}
+
 // IgnitionModule::update: spark when the cycle angle passes
 // firingAngle - timingCurve(|omega|); suppressed while the rev limiter timer runs or
 // ignition is off (BridgeSimulator.cpp:191-195).
@@ -37,9 +59,12 @@ void Engine::ignitionUpdate() {
                     const double u = esb_rand_u01(seed, ESB_STREAM_BURN + i, igniteCount[i]);
                     igniteCount[i] += 1;
                     const double rnd = P.burningEfficiencyRandomness;
-                    f.efficiency = P.maxBurningEfficiency * (rnd * u + (1.0 - rnd));
                     const double meanPistonSpeed = 2.0 * (2.0 * P.crankThrow) * (speed / (2.0 * kPi));
                     const double turbulence = sampleTriangle(P, P.cyl[i].fnMeanPistonSpeedToTurbulence, meanPistonSpeed);
+                    // Fuel parameters the reference requires and forwards (FuelDeserializer.cpp:26-39): a burn in a slow,
+                    // residual-laden charge is less complete (ASSUMPTIONS.md #7)
+                    f.efficiency = P.maxBurningEfficiency * (rnd * u + (1.0 - rnd)) *
+                                   burnQuality(turbulence, g.mix.p_inert, g.mix.p_o2, P.lowEfficiencyAttenuation, P.maxTurbulenceEffect, P.maxDilutionEffect);
                     const double ratio = sampleTriangle(P, P.fnTurbulenceToFlameSpeedRatio, turbulence);
                     f.flameSpeed = 2.0 * ratio; // laminar speed 2 m/s (ASSUMPTIONS.md #7)
                     f.lit = true; f.travel_x = 0; f.travel_y = 0; f.lastVolume = 0;

@@ -130,7 +130,15 @@ void Engine::placeBodies() {
     for (int i = 0; i < N; ++i) {
         const EsbCylinder &c = P.cyl[i];
         const double phi = P.journalAngle[c.journal];
-        const double jx = P.crankPosX + P.crankThrow * esb_cos(phi), jy = P.crankPosY + P.crankThrow * esb_sin(phi);
+        double jx = P.crankPosX + P.crankThrow * esb_cos(phi), jy = P.crankPosY + P.crankThrow * esb_sin(phi);
+        if (c.masterCylinder >= 0) {   // slave rod: its journal sits on the (already placed) master rod
+            const EsbCylinder &mc = P.cyl[c.masterCylinder];
+            const Body &m = bodies[2 + 2 * c.masterCylinder];
+            const double lx = -esb_sin(c.slaveJournalAngle) * mc.slaveThrow;
+            const double ly = -(0.5 * mc.rodLength + mc.rodCenterOfMass) + esb_cos(c.slaveJournalAngle) * mc.slaveThrow;
+            const double sM = esb_sin(m.th), cM = esb_cos(m.th);
+            jx = m.px + (cM * lx - sM * ly); jy = m.py + (sM * lx + cM * ly);
+        }
         const double dx = -esb_sin(c.bankAngle), dy = esb_cos(c.bankAngle);
         const double nx = dy, ny = -dx;
         const double rx = jx - c.bankX, ry = jy - c.bankY;

@@ -78,9 +78,27 @@ void Engine::buildRows() {
             geometric(ry, (rb.py + a.y) - (pb.py + pin.y), -(rb.w * rb.w) * a.y + (pb.w * pb.w) * pin.y);
             rows.push_back(ry);
         }
+        const Rot b = rotate(sR, cR, 0.0, bigEnd);
+        if (c.masterCylinder >= 0) {
+            // slave rod (radial engines, 09_radial_9.mr:145-165): LinkConstraint master rod <-> this rod; the journal is a
+            // point of the master rod at slaveThrow from its big end
+            const EsbCylinder &mc = P.cyl[c.masterCylinder];
+            const int mi = 2 + 2 * c.masterCylinder;
+            const Body &mb = bodies[mi];
+            double sM, cM; esb_sincos(mb.th, &sM, &cM);
+            double sA, cA; esb_sincos(c.slaveJournalAngle, &sA, &cA);
+            const double masterBigEnd = -(0.5 * mc.rodLength + mc.rodCenterOfMass);
+            const Rot j = rotate(sM, cM, -sA * mc.slaveThrow, masterBigEnd + cA * mc.slaveThrow);
+            Row rx; rx.b0 = mi; rx.b1 = ri; rx.J0[0] = 1; rx.J0[2] = -j.y; rx.J1[0] = -1; rx.J1[2] = b.y;
+            geometric(rx, (mb.px + j.x) - (rb.px + b.x), -(mb.w * mb.w) * j.x + (rb.w * rb.w) * b.x);
+            rows.push_back(rx);
+            Row ry; ry.b0 = mi; ry.b1 = ri; ry.J0[1] = 1; ry.J0[2] = j.x; ry.J1[1] = -1; ry.J1[2] = -b.x;
+            geometric(ry, (mb.py + j.y) - (rb.py + b.y), -(mb.w * mb.w) * j.y + (rb.w * rb.w) * b.y);
+            rows.push_back(ry);
+            continue;
+        }
         double sJ, cJ; esb_sincos(P.journalAngle[c.journal], &sJ, &cJ);
         const Rot j = rotate(sC, cC, P.crankThrow * cJ, P.crankThrow * sJ);
-        const Rot b = rotate(sR, cR, 0.0, bigEnd);
         { // rod journal: A = crank (j), B = rod (b)
             Row rx; rx.b0 = 0; rx.b1 = ri; rx.J0[0] = 1; rx.J0[2] = -j.y; rx.J1[0] = -1; rx.J1[2] = b.y;
             geometric(rx, (crank.px + j.x) - (rb.px + b.x), -(crank.w * crank.w) * j.x + (rb.w * rb.w) * b.x);

@@ -39,6 +39,7 @@ SCRIPTS = {
     "ferrari_f136": "es/engines/atg-video-2/08_ferrari_f136_v8.mr",
     "lfa_v10": "es/engines/atg-video-2/10_lfa_v10.mr",
     "merlin_v12": "es/engines/atg-video-2/11_merlin_v12.mr",
+    "radial_9": "es/engines/atg-video-2/09_radial_9.mr",   # master / slave connecting rods (BASELINE config 4)
     "hayabusa_i4": "es/engines/atg-video-1/04_hayabusa.mr",
     "default_v8": "es/main.mr",   # the bridge's default script (BASELINE config 1): main.mr -> v8_engine.mr "Simple V8"
 }
@@ -68,6 +69,14 @@ def main():
         ir = read_wav_mono16(os.path.join(REF, "es", irs[0]))
         np.save(os.path.join(HERE, name + ".ir.npy"), ir)
         print(name, r.stdout.splitlines()[0], "ir", irs[0], len(ir))
+    # gm_ls with evacuated chambers at the start: gas exchanges with an empty cell, i.e. the exact-arithmetic path of the kernel
+    import json as _json
+    doc = _json.load(open(os.path.join(REF, PRESETS["gm_ls"])))
+    for ch in doc["engine"]["combustionChambers"]:
+        ch["startingPressure"] = 0.0
+    tmp = os.path.join(build, "gm_ls_evacuated.preset.json")
+    _json.dump(doc, open(tmp, "w"))
+    subprocess.run([exe, tmp, os.path.join(HERE, "gm_ls_evacuated.params.bin")], check=True, capture_output=True, text=True)
     import importlib.util
     import json
     spec = importlib.util.spec_from_file_location("mr_frontend", os.path.join(ROOT, "engine-sim-cli_b200", "mr_frontend.py"))

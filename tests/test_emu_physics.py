@@ -51,3 +51,11 @@ def test_emu_single_matches_oracle(honda_blob):
 def test_emu_result_independent_of_lane_count(subaru_blob):
     # 4 cylinders on 8 lanes (4 idle lanes) gives the same bits as on 4 lanes
     _compare(subaru_blob, 120, 1500.0, 0.5, seed=1, lanes=8)
+
+
+def test_emu_radial_master_slave_rods_match_oracle():
+    """Radial 9 (09_radial_9.mr): eight slave rods ride on journals of the master rod; 9 cylinders on 16 lanes."""
+    import os
+    from conftest import GOLDEN
+    blob = open(os.path.join(GOLDEN, "radial_9.params.bin"), "rb").read()
+    _compare(blob, 150, 1500.0, 0.8, seed=3)

@@ -330,7 +330,8 @@ def test_fir_microbench_script(tmp_path):
     assert line["value"] > 1.0
 
 
-@pytest.mark.parametrize("name,n,steps", [("ferrari_f136", 6, 500), ("lfa_v10", 5, 400), ("merlin_v12", 3, 400), ("hayabusa_i4", 9, 400), ("default_v8", 4, 400)])
+@pytest.mark.parametrize("name,n,steps", [("ferrari_f136", 6, 500), ("lfa_v10", 5, 400), ("merlin_v12", 3, 400), ("hayabusa_i4", 9, 400), ("default_v8", 4, 400),
+                                          ("radial_9", 5, 600)])
 def test_mr_script_engines_bit_exact(name, n, steps):
     """Engines that exist only as .mr scripts, compiled by the front-end (mr_frontend.py -> tests/golden/*.params.bin):
     BASELINE configs 3-4's F136 / LFA V10 / Merlin V12 (10 and 12 cylinders run on 16 lanes per instance) and an inline four

@@ -119,10 +119,6 @@ def test_every_engine_script_compiles():
         base = os.path.basename(p)
         if base in ("radial.mr", "M156.mr"):       # libraries without a main node
             continue
-        if "radial" in base:
-            with pytest.raises(m.MrError, match="master / slave"):
-                m.compile_script(p)
-            continue
         if "kohler" in base:                        # the only script with a speed governor instead of a throttle linkage
             with pytest.raises(m.MrError, match="governor"):
                 m.compile_script(p)
@@ -132,7 +128,14 @@ def test_every_engine_script_compiles():
         assert len(e["ignitionModule"]["firingOrder"]) == e["cylinderCount"]
         names[base] = (e["name"], e["cylinderCount"])
     assert names["08_ferrari_f136_v8.mr"] == ("Ferrari F136", 8) and names["10_lfa_v10.mr"][1] == 10 and names["11_merlin_v12.mr"][1] == 12
-    assert len(names) >= 17
+    assert len(names) >= 19
+    # radial engines: one master rod on the crankshaft, every other rod on a journal of the master (09_radial_9.mr:145-165)
+    e = m.compile_script(os.path.join(REF, "es", "engines", "atg-video-2", "09_radial_9.mr"))["engine"]
+    rods = [b["cylinders"][0]["connectingRod"] for b in e["cylinderBanks"]]
+    assert [r["masterCylinder"] for r in rods] == [-1] + [0] * 8
+    assert rods[0]["slaveThrow"] == pytest.approx(3.5 * 0.0254) and rods[0]["length"] == pytest.approx(16 * 0.0254)
+    assert all(r["length"] == pytest.approx(12.5 * 0.0254) for r in rods[1:])
+    assert [r["slaveJournalAngle"] for r in rods[1:]] == pytest.approx([k / 9.0 * 2 * 3.141592653589793 for k in range(1, 9)])
 
 
 @needs_ref
