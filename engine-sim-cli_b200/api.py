@@ -55,6 +55,29 @@ def _get_layout():
     return _layout
 
 
+def script_library_root(script_path):
+    """The directory above the script that holds engine_sim.mr (and sound-library/), or None."""
+    d = os.path.dirname(os.path.abspath(script_path))
+    while d and d != os.path.dirname(d):
+        if os.path.isfile(os.path.join(d, "engine_sim.mr")):
+            return d
+        d = os.path.dirname(d)
+    return None
+
+
+def compile_script(script_path):
+    """Engine script -> preset document (dict), by the library's front-end (EsbCompileScript)."""
+    import json
+    n = C.c_int64()
+    rc = lib().EsbCompileScript(script_path.encode(), None, 0, C.byref(n))
+    if rc != ESIM_SUCCESS:
+        msg = lib().EsbBatchGetLastError(None)
+        raise EngineSimError(rc, "script compilation failed: " + (msg.decode() if msg else ""))
+    buf = C.create_string_buffer(n.value + 1)
+    lib().EsbCompileScript(script_path.encode(), buf, n.value + 1, C.byref(n))
+    return json.loads(buf.value.decode())
+
+
 def params_size():
     return _get_layout()[0]
 
@@ -84,7 +107,11 @@ def lib():
             "EsbBatchGetLastStream": [vp, vp, i32, C.POINTER(i32)], "EsbBatchGetStats": [vp, i32, vp], "EsbBatchWriteWavs": [vp, C.c_char_p, C.c_char_p],
             "EsbBatchSetLaunchConfig": [vp, i32, i32], "EsbBatchGetLaunchCounts": [vp, vp],
             "EsbBatchSetProfiling": [vp, i32], "EsbBatchSetPhysicsShape": [vp, i32, i32], "EsbBatchGetKernelTimes": [vp, vp, vp],
-            "EsbFirRun": [vp, i64, i64, vp, i32, i32, i32, i32, i64, vp, i64, vp], "EsbProbePeak": [i32, i32, C.POINTER(dbl)], "EsbGetLayout": [C.POINTER(i32), C.POINTER(i32)],
+            "EsbFirRun": [vp, i64, i64, vp, i32, i32, i32, i32, i64, vp, i64, vp], "EsbProbePeak": [i32, i32, C.POINTER(dbl)], "EsbGetLayout": [C.POINTER(i32), C.POINTER(i32)], "EsbCompileScript": [C.c_char_p, C.c_char_p, i64, C.POINTER(i64)],
+            "EsbMultiCreate": [i32, vp, vp, vp, C.POINTER(vp)], "EsbMultiDestroy": [vp], "EsbMultiGetShardBatch": [vp, i32, C.POINTER(vp)],
+            "EsbMultiLoadEngineFile": [vp, i32, C.c_char_p, C.c_char_p], "EsbMultiLoadParams": [vp, i32, vp],
+            "EsbMultiSetImpulseResponse": [vp, i32, i32, vp, i32, flt, i32], "EsbMultiSamplesFor": [vp, i32, C.POINTER(i32)],
+            "EsbMultiRender": [vp, i32, vp, i64, vp], "EsbMultiWriteWavs": [vp, C.c_char_p, C.c_char_p], "EsbMultiGetStats": [vp, i32, vp],
             "EsbCheckFastArith": [i32, i32, vp, vp, vp, vp],
             "EngineSimCreate": [vp, C.POINTER(vp)], "EngineSimLoadScript": [vp, C.c_char_p, C.c_char_p], "EngineSimLoadParams": [vp, vp, vp, i32, flt],
             "EngineSimDestroy": [vp], "EngineSimSetThrottle": [vp, dbl], "EngineSimSetSpeedControl": [vp, dbl], "EngineSimSetIgnition": [vp, i32],
@@ -99,6 +126,8 @@ def lib():
             fn.restype = i32
         L.EsbBatchGetLastError.argtypes = [vp]
         L.EsbBatchGetLastError.restype = C.c_char_p
+        L.EsbMultiGetLastError.argtypes = [vp]
+        L.EsbMultiGetLastError.restype = C.c_char_p
         L.EngineSimGetLastError.argtypes = [vp]
         L.EngineSimGetLastError.restype = C.c_char_p
         L.EngineSimGetVersion.restype = C.c_char_p
@@ -137,9 +166,18 @@ class BatchSimulator:
             msg = lib().EsbBatchGetLastError(self.h)
             raise EngineSimError(rc, msg.decode() if msg else "")
 
+    @classmethod
+    def _borrowed(cls, handle, n_instances, owner):
+        """A view of a batch handle someone else owns (a shard of MultiBatchSimulator)."""
+        self = cls.__new__(cls)
+        self.h, self.n, self.channels, self.sample_rate = handle, int(n_instances), 0, 44100
+        self._owner = owner
+        return self
+
     def close(self):
         if getattr(self, "h", None):
-            lib().EsbBatchDestroy(self.h)
+            if getattr(self, "_owner", None) is None:
+                lib().EsbBatchDestroy(self.h)
             self.h = None
 
     def __del__(self):
@@ -163,26 +201,16 @@ class BatchSimulator:
         self._check(lib().EsbBatchLoadPresetJson(self.h, text.encode()))
 
     def load_script(self, path, asset_base=None):
-        """Loads an engine from a preset JSON or an engine-sim `.mr` script (compiled by mr_frontend.py; the impulse
-        responses the script names are read from `asset_base`/sound-library, by default the script library's root)."""
-        if not path.endswith(".mr"):
-            return self.load_preset_file(path, asset_base)
-        import json
-        import tempfile
+        """Loads an engine from a preset JSON or an engine-sim `.mr` script (compiled inside the library, csrc/mr_script.cpp; the
+        impulse responses the script names are read from `asset_base`/sound-library, by default the script library's root)."""
+        if asset_base is None and not path.endswith(".json"):
+            asset_base = script_library_root(path)
+        self.load_preset_file(path, asset_base)
 
-        from . import mr_frontend
-        try:
-            doc = mr_frontend.compile_script(path)
-        except mr_frontend.MrError as e:
-            raise EngineSimError(-6, f"script compilation failed: {e}") from e       # ESIM_ERROR_SCRIPT_COMPILATION
-        if asset_base is None:
-            asset_base = mr_frontend.library_root(path)
-        with tempfile.NamedTemporaryFile("w", suffix=".preset.json", delete=False) as f:
-            json.dump(doc, f)
-        try:
-            self.load_preset_file(f.name, asset_base)
-        finally:
-            os.unlink(f.name)
+    def impulse_response_taps(self, exhaust):
+        taps = C.c_int32()
+        self._check(lib().EsbBatchGetImpulseResponseTaps(self.h, exhaust, C.byref(taps)))
+        return taps.value
 
     def set_impulse_response(self, exhaust, samples_s16, volume, max_taps=0):
         s = np.ascontiguousarray(samples_s16, dtype=np.int16)
@@ -308,6 +336,92 @@ class BatchSimulator:
         return [int(x) for x in c]
 
 
+class MultiBatchSimulator:
+    """The job's instances sharded over several GPUs of one box (EsbMulti* functions): device d holds a contiguous block, every
+    instance keeps its global index (noise seed, controls, PCM row, WAV name), no collective on the path.  `shards[d]` is the
+    ordinary BatchSimulator view of device d for everything this layer does not wrap (schedules, telemetry renders, state)."""
+
+    def __init__(self, n_instances, devices, sim_freq=0, seed=0, counts=None, fluid_steps=8, sample_rate=44100, air_noise=-1.0):
+        L = lib()
+        devices = [int(d) for d in devices]
+        if counts is None:
+            per = -(-int(n_instances) // len(devices))
+            counts = [max(0, min(per, int(n_instances) - k * per)) for k in range(len(devices))]
+        assert sum(counts) == n_instances and len(counts) == len(devices)
+        cfg = EngineSimConfig(sampleRate=sample_rate, inputBufferSize=44100, audioBufferSize=44100, simulationFrequency=int(sim_freq),
+                              fluidSimulationSteps=fluid_steps, maxChunkFrames=4096, targetSynthesizerLatency=0.02, volume=0.5,
+                              convolutionLevel=0.5, airNoise=air_noise, seed=seed)
+        dev = (C.c_int32 * len(devices))(*devices)
+        cnt = (C.c_int32 * len(devices))(*[int(c) for c in counts])
+        self.h = C.c_void_p()
+        rc = L.EsbMultiCreate(len(devices), dev, cnt, C.byref(cfg), C.byref(self.h))
+        if rc != ESIM_SUCCESS:
+            msg = L.EsbMultiGetLastError(None)
+            raise EngineSimError(rc, msg.decode() if msg else "create failed")
+        self.n, self.devices, self.counts = int(n_instances), devices, [int(c) for c in counts]
+        self.first = [int(x) for x in np.cumsum([0] + self.counts[:-1])]
+        self.shards = []
+        for k in range(len(devices)):
+            hk = C.c_void_p()
+            self._check(L.EsbMultiGetShardBatch(self.h, k, C.byref(hk)))
+            self.shards.append(BatchSimulator._borrowed(hk, self.counts[k], self))
+
+    def _check(self, rc):
+        if rc != ESIM_SUCCESS:
+            msg = lib().EsbMultiGetLastError(self.h)
+            raise EngineSimError(rc, msg.decode() if msg else "")
+
+    def close(self):
+        if getattr(self, "h", None):
+            for s in self.shards:
+                s.h = None
+            lib().EsbMultiDestroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def load_script(self, path, asset_base=None, shard=-1):
+        if asset_base is None and not path.endswith(".json"):
+            asset_base = script_library_root(path)
+        self._check(lib().EsbMultiLoadEngineFile(self.h, shard, path.encode(), asset_base.encode() if asset_base else None))
+
+    def load_params(self, blob, shard=-1):
+        buf = C.create_string_buffer(blob, len(blob))
+        self._check(lib().EsbMultiLoadParams(self.h, shard, buf))
+
+    def set_impulse_response(self, exhaust, samples_s16, volume, max_taps=0, shard=-1):
+        s = np.ascontiguousarray(samples_s16, dtype=np.int16)
+        self._check(lib().EsbMultiSetImpulseResponse(self.h, shard, exhaust, _ptr(s), len(s), float(volume), int(max_taps)))
+
+    def set_controls(self, **kw):
+        """Same keywords as BatchSimulator.set_controls; arrays are indexed by the job's global instance index."""
+        for k, sh in enumerate(self.shards):
+            lo, hi = self.first[k], self.first[k] + self.counts[k]
+            part = {key: (np.asarray(v)[lo:hi] if np.ndim(v) > 0 else v) for key, v in kw.items()}
+            sh.set_controls(**part)
+
+    def render(self, n_steps, want_pcm=True):
+        """All devices at once.  Returns (pcm int16 [n, max samples] or None, samples per instance of each shard)."""
+        m = C.c_int32()
+        self._check(lib().EsbMultiSamplesFor(self.h, n_steps, C.byref(m)))
+        pcm = np.zeros((self.n, max(m.value, 1)), dtype=np.int16) if want_pcm else None
+        produced = (C.c_int32 * len(self.devices))()
+        self._check(lib().EsbMultiRender(self.h, n_steps, _ptr(pcm), pcm.shape[1] if pcm is not None else 0, produced))
+        return pcm, [int(x) for x in produced]
+
+    def write_wavs(self, directory, prefix="engine_"):
+        self._check(lib().EsbMultiWriteWavs(self.h, directory.encode(), prefix.encode()))
+
+    def stats(self, instance):
+        s = EngineSimStats()
+        self._check(lib().EsbMultiGetStats(self.h, instance, C.byref(s)))
+        return s
+
+
 class Simulator:
     """ISimulator / ICombustionEngine mirror (engine-sim-bridge/include/simulator/ISimulator.h:12-45) over EngineSim*."""
 
@@ -339,26 +453,10 @@ class Simulator:
         return msg.decode() if msg else ""
 
     def load_script(self, path, asset_base=None):
-        """EngineSimLoadScript: a preset JSON directly; an engine-sim `.mr` script is compiled first (mr_frontend.py)."""
-        tmp = None
-        if path.endswith(".mr"):
-            import json
-            import tempfile
-
-            from . import mr_frontend
-            try:
-                doc = mr_frontend.compile_script(path)
-            except mr_frontend.MrError as e:
-                raise EngineSimError(-6, f"script compilation failed: {e}") from e   # ESIM_ERROR_SCRIPT_COMPILATION
-            asset_base = asset_base or mr_frontend.library_root(path)
-            with tempfile.NamedTemporaryFile("w", suffix=".preset.json", delete=False) as f:
-                json.dump(doc, f)
-            path = tmp = f.name
-        try:
-            self._check(lib().EngineSimLoadScript(self.h, path.encode(), asset_base.encode() if asset_base else None))
-        finally:
-            if tmp:
-                os.unlink(tmp)
+        """EngineSimLoadScript: a preset JSON, or an engine-sim `.mr` script compiled by the library's own front-end."""
+        if asset_base is None and not path.endswith(".json"):
+            asset_base = script_library_root(path)
+        self._check(lib().EngineSimLoadScript(self.h, path.encode(), asset_base.encode() if asset_base else None))
 
     def load_params(self, blob, ir=None, ir_volume=0.001):
         buf = C.create_string_buffer(blob, len(blob))

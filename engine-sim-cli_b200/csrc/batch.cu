@@ -589,7 +589,7 @@ int Batch::writeWavs(const char *dir, const char *prefix) {
     ESB_CUDA(cudaStreamSynchronize(stream));
     for (int i = 0; i < nInst; ++i) {
         char name[1024];
-        std::snprintf(name, sizeof(name), "%s/%s%05d.wav", dir, prefix ? prefix : "engine_", i);
+        std::snprintf(name, sizeof(name), "%s/%s%05d.wav", dir, prefix ? prefix : "engine_", wavIndexBase + i);
         std::string err;
         if (!writeWavMono16(name, h.data() + (size_t)i * lastRenderCount, lastRenderCount, cfg.sampleRate, err)) { lastError = err; return ESIM_ERROR_LOAD_FAILED; }
     }

@@ -40,6 +40,7 @@ class Batch {
     void setProfiling(bool on) { profiling = on; }
     int kernelTimes(double ms[4], long long launches[4]);
 
+    int wavIndexBase = 0;   // number of the first instance in file names (a shard of a multi-device batch starts at its global index)
     std::string lastError;
     EngineSimConfig cfg{};
     EsbEngineParams params{};

@@ -9,6 +9,7 @@
 #include <deque>
 #include <memory>
 #include <new>
+#include <thread>
 
 using esb::Batch;
 
@@ -30,6 +31,7 @@ int guardBatch(EsbBatchHandle h) { return h ? ESIM_SUCCESS : ESIM_ERROR_INVALID_
 
 template <typename F> int guarded(Batch &b, F &&f) {
     try { return f(); }
+    catch (const esb::ScriptError &e) { b.lastError = e.what(); return ESIM_ERROR_SCRIPT_COMPILATION; }
     catch (const std::exception &e) { b.lastError = e.what(); return ESIM_ERROR_LOAD_FAILED; }
     catch (...) { b.lastError = "unknown error"; return ESIM_ERROR_LOAD_FAILED; }
 }
@@ -79,7 +81,20 @@ int32_t EsbBatchLoadPresetJson(EsbBatchHandle h, const char *json) {
 int32_t EsbBatchLoadPresetFile(EsbBatchHandle h, const char *path, const char *assetBase) {
     if (!h) return ESIM_ERROR_INVALID_HANDLE;
     if (!path) return ESIM_ERROR_INVALID_PARAMETER;
-    return guarded(h->b, [&] { esb::LoadedPreset lp; esb::loadPresetFile(path, lp); return loadPresetInto(h->b, lp, assetBase); });
+    return guarded(h->b, [&] { esb::LoadedPreset lp; esb::loadEngineFile(path, lp); return loadPresetInto(h->b, lp, assetBase); });
+}
+int32_t EsbCompileScript(const char *scriptPath, char *outJson, int64_t capacity, int64_t *outLength) {
+    if (!scriptPath || !outLength) return ESIM_ERROR_INVALID_PARAMETER;
+    try {
+        const std::string doc = esb::compileScriptToPresetJson(scriptPath, {});
+        *outLength = (int64_t)doc.size();
+        if (outJson && capacity > 0) {
+            const size_t n = std::min<size_t>(doc.size(), (size_t)capacity - 1);
+            std::memcpy(outJson, doc.data(), n);
+            outJson[n] = 0;
+        }
+        return ESIM_SUCCESS;
+    } catch (const std::exception &e) { g_createError = e.what(); return ESIM_ERROR_SCRIPT_COMPILATION; }
 }
 int32_t EsbBatchLoadParams(EsbBatchHandle h, const EsbEngineParams *p) {
     if (!h) return ESIM_ERROR_INVALID_HANDLE;
@@ -266,12 +281,9 @@ int32_t EngineSimLoadScript(EngineSimHandle h, const char *scriptPath, const cha
     if (!h) return ESIM_ERROR_INVALID_HANDLE;
     if (!scriptPath) { h->b.lastError = "scriptPath is null"; return ESIM_ERROR_INVALID_PARAMETER; }
     const std::string p(scriptPath);
-    if (p.size() >= 3 && p.compare(p.size() - 3, 3, ".mr") == 0) {
-        h->b.lastError = "'.mr' scripts are compiled by the host-side front-end (engine_sim_cli_b200/mr_frontend.py -> preset JSON; the Python API's load_script does it); pass the resulting preset JSON here";
-        return ESIM_ERROR_SCRIPT_COMPILATION;
-    }
     h->computed.clear(); h->released = 0;
-    return guarded(h->b, [&] { esb::LoadedPreset lp; esb::loadPresetFile(p, lp); return loadPresetInto(h->b, lp, assetBase); });
+    // "*.json" -> preset document, anything else -> engine script (SimulatorFactory.cpp:111-156)
+    return guarded(h->b, [&] { esb::LoadedPreset lp; esb::loadEngineFile(p, lp); return loadPresetInto(h->b, lp, assetBase); });
 }
 int32_t EngineSimLoadParams(EngineSimHandle h, const EsbEngineParams *params, const int16_t *ir, int32_t irCount, float irVolume) {
     if (!h) return ESIM_ERROR_INVALID_HANDLE;
@@ -395,6 +407,157 @@ int32_t EngineSimGetSimulationFrequency(EngineSimHandle h, int32_t *out) {
     if (!h) return ESIM_ERROR_INVALID_HANDLE;
     if (!out) return ESIM_ERROR_INVALID_PARAMETER;
     *out = (int32_t)h->b.simFreq;
+    return ESIM_SUCCESS;
+}
+
+} // extern "C"
+
+// ---------------------------------------------------------------------------------------
+// multi-device batch: instances sharded over the GPUs of one box, no collective on the path
+// (north_star: "each GPU writes its own WAVs and per-instance telemetry, gathered once to the host at the end";
+// SURVEY.md §8(b) EsbBatchCreate(n, device_ids[], cfg), §8(e)).  One Batch per device, one host thread per device
+// while rendering; instance i of the job keeps its global index for seeds, controls, output rows and file names.
+struct EsbMultiOpaque {
+    std::vector<std::unique_ptr<EsbBatchOpaque>> shard;   // each shard is an ordinary batch handle, owned here
+    std::vector<int> first, count;     // global index of each shard's first instance, its size
+    int nInst = 0;
+    std::string lastError;
+    int shardOf(int inst) const { for (size_t s = 0; s < shard.size(); ++s) if (inst >= first[s] && inst < first[s] + count[s]) return (int)s; return -1; }
+};
+namespace {
+template <typename F> int forEachShard(EsbMultiOpaque *m, int only, F &&f) {
+    for (size_t s = 0; s < m->shard.size(); ++s) {
+        if (only >= 0 && (int)s != only) continue;
+        const int rc = f(m->shard[s]->b, (int)s);
+        if (rc != ESIM_SUCCESS) { m->lastError = "device " + std::to_string(m->shard[s]->b.device) + ": " + m->shard[s]->b.lastError; return rc; }
+    }
+    return ESIM_SUCCESS;
+}
+// runs f on every shard concurrently, one host thread per device
+template <typename F> int parallelShards(EsbMultiOpaque *m, F &&f) {
+    std::vector<int> rc(m->shard.size(), ESIM_SUCCESS);
+    std::vector<std::thread> th;
+    for (size_t s = 0; s < m->shard.size(); ++s) th.emplace_back([&, s] { rc[s] = f(m->shard[s]->b, (int)s); });
+    for (auto &t : th) t.join();
+    for (size_t s = 0; s < rc.size(); ++s)
+        if (rc[s] != ESIM_SUCCESS) { m->lastError = "device " + std::to_string(m->shard[s]->b.device) + ": " + m->shard[s]->b.lastError; return rc[s]; }
+    return ESIM_SUCCESS;
+}
+} // namespace
+
+extern "C" {
+
+int32_t EsbMultiCreate(int32_t nDevices, const int32_t *deviceIds, const int32_t *instancesPerDevice, const EngineSimConfig *cfg, EsbMultiHandle *out) {
+    if (!out) return ESIM_ERROR_INVALID_PARAMETER;
+    *out = nullptr;
+    if (nDevices <= 0 || !deviceIds || !instancesPerDevice) { g_createError = "device list and per-device instance counts are required"; return ESIM_ERROR_INVALID_PARAMETER; }
+    std::unique_ptr<EsbMultiOpaque> m(new EsbMultiOpaque());
+    int first = 0;
+    for (int d = 0; d < nDevices; ++d) {
+        if (instancesPerDevice[d] <= 0) { g_createError = "every device needs at least one instance"; return ESIM_ERROR_INVALID_PARAMETER; }
+        EngineSimConfig c{};
+        if (cfg) c = *cfg;
+        c.seed = (cfg ? cfg->seed : 0u) + (uint32_t)first;   // instance i of the job draws noise with seed + i whatever the sharding
+        std::unique_ptr<EsbBatchOpaque> b(new EsbBatchOpaque());
+        const int rc = b->b.create(instancesPerDevice[d], deviceIds[d], &c);
+        if (rc != ESIM_SUCCESS) { g_createError = "device " + std::to_string(deviceIds[d]) + ": " + b->b.lastError; return rc; }
+        b->b.wavIndexBase = first;
+        m->first.push_back(first); m->count.push_back(instancesPerDevice[d]);
+        m->shard.push_back(std::move(b));
+        first += instancesPerDevice[d];
+    }
+    m->nInst = first;
+    *out = m.release();
+    return ESIM_SUCCESS;
+}
+int32_t EsbMultiDestroy(EsbMultiHandle m) { delete m; return ESIM_SUCCESS; }
+const char *EsbMultiGetLastError(EsbMultiHandle m) { return m ? m->lastError.c_str() : g_createError.c_str(); }
+int32_t EsbMultiGetShard(EsbMultiHandle m, int32_t shard, int32_t *outDevice, int32_t *outFirst, int32_t *outCount) {
+    if (!m) return ESIM_ERROR_INVALID_HANDLE;
+    if (shard < 0 || shard >= (int)m->shard.size()) return ESIM_ERROR_INVALID_PARAMETER;
+    if (outDevice) *outDevice = m->shard[shard]->b.device;
+    if (outFirst) *outFirst = m->first[shard];
+    if (outCount) *outCount = m->count[shard];
+    return ESIM_SUCCESS;
+}
+// shard < 0: every device gets the same engine; else only that shard (one engine type per GPU, the mixed sweep of BASELINE config 4)
+int32_t EsbMultiLoadEngineFile(EsbMultiHandle m, int32_t shard, const char *path, const char *assetBase) {
+    if (!m) return ESIM_ERROR_INVALID_HANDLE;
+    if (!path || shard >= (int)m->shard.size()) return ESIM_ERROR_INVALID_PARAMETER;
+    esb::LoadedPreset lp;
+    try { esb::loadEngineFile(path, lp); }
+    catch (const esb::ScriptError &e) { m->lastError = e.what(); return ESIM_ERROR_SCRIPT_COMPILATION; }
+    catch (const std::exception &e) { m->lastError = e.what(); return ESIM_ERROR_LOAD_FAILED; }
+    return forEachShard(m, shard, [&](Batch &b, int) { return guarded(b, [&] { return loadPresetInto(b, lp, assetBase); }); });
+}
+int32_t EsbMultiLoadParams(EsbMultiHandle m, int32_t shard, const EsbEngineParams *p) {
+    if (!m) return ESIM_ERROR_INVALID_HANDLE;
+    if (!p || shard >= (int)m->shard.size()) return ESIM_ERROR_INVALID_PARAMETER;
+    return forEachShard(m, shard, [&](Batch &b, int) { return guarded(b, [&] { return b.loadParams(*p); }); });
+}
+int32_t EsbMultiSetImpulseResponse(EsbMultiHandle m, int32_t shard, int32_t exhaust, const int16_t *s, int32_t n, float volume, int32_t maxTaps) {
+    if (!m) return ESIM_ERROR_INVALID_HANDLE;
+    if (shard >= (int)m->shard.size()) return ESIM_ERROR_INVALID_PARAMETER;
+    return forEachShard(m, shard, [&](Batch &b, int) { return b.setImpulseResponse(exhaust, s, n, volume, maxTaps); });
+}
+// controls of the job's instances [first, first + count), global indices
+int32_t EsbMultiSetControls(EsbMultiHandle m, int32_t first, int32_t count, const EsbControls *c) {
+    if (!m) return ESIM_ERROR_INVALID_HANDLE;
+    if (first < 0 || count < 0 || first + count > m->nInst || !c) { m->lastError = "control range out of bounds"; return ESIM_ERROR_INVALID_PARAMETER; }
+    return forEachShard(m, -1, [&](Batch &b, int s) {
+        const int lo = std::max(first, m->first[s]), hi = std::min(first + count, m->first[s] + m->count[s]);
+        if (lo >= hi) return (int)ESIM_SUCCESS;
+        return b.setControls(lo - m->first[s], hi - lo, c + (lo - first));
+    });
+}
+int32_t EsbMultiSamplesFor(EsbMultiHandle m, int32_t nSteps, int32_t *outMax) {
+    if (!m) return ESIM_ERROR_INVALID_HANDLE;
+    if (!outMax) return ESIM_ERROR_INVALID_PARAMETER;
+    int best = 0;
+    for (auto &h : m->shard) {
+        Batch &b = h->b;
+        if (!b.loaded) { m->lastError = "no engine loaded on device " + std::to_string(b.device); return ESIM_ERROR_NOT_INITIALIZED; }
+        int k = 0;
+        b.samplesFor(nSteps, &k);
+        best = std::max(best, k);
+    }
+    *outMax = best;
+    return ESIM_SUCCESS;
+}
+// Advances every instance by nSteps on its own device, all devices at once.  pcm: host [nInstances][pcmStride] int16 in global
+// instance order or NULL (audio stays on the devices: EsbMultiWriteWavs); outSamples: [nDevices] samples produced per instance
+// of each shard (shards may run different engines at different simulation frequencies).
+int32_t EsbMultiRender(EsbMultiHandle m, int32_t nSteps, int16_t *pcm, int64_t pcmStride, int32_t *outSamples) {
+    if (!m) return ESIM_ERROR_INVALID_HANDLE;
+    return parallelShards(m, [&](Batch &b, int s) {
+        int produced = 0;
+        const int rc = b.render(nSteps, pcm ? pcm + (size_t)m->first[s] * pcmStride : nullptr, nullptr, pcmStride, &produced, nullptr, 0);
+        if (outSamples) outSamples[s] = produced;
+        if (rc == ESIM_SUCCESS && !pcm) cudaStreamSynchronize(b.stream);
+        return rc;
+    });
+}
+// every device writes the WAVs of its own instances (engine_<global index>.wav), concurrently
+int32_t EsbMultiWriteWavs(EsbMultiHandle m, const char *dir, const char *prefix) {
+    if (!m) return ESIM_ERROR_INVALID_HANDLE;
+    if (!dir) return ESIM_ERROR_INVALID_PARAMETER;
+    return parallelShards(m, [&](Batch &b, int) { return b.writeWavs(dir, prefix); });
+}
+// telemetry gathered once at the end: EngineSimStats of every instance, global order
+int32_t EsbMultiGetStats(EsbMultiHandle m, int32_t inst, EngineSimStats *out) {
+    if (!m) return ESIM_ERROR_INVALID_HANDLE;
+    const int s = m->shardOf(inst);
+    if (s < 0 || !out) { m->lastError = "instance out of range"; return ESIM_ERROR_INVALID_PARAMETER; }
+    const int rc = m->shard[s]->b.getStats(inst - m->first[s], out);
+    if (rc != ESIM_SUCCESS) m->lastError = m->shard[s]->b.lastError;
+    return rc;
+}
+int32_t EsbMultiGetShardBatch(EsbMultiHandle m, int32_t shard, EsbBatchHandle *out) {
+    // the per-device batch for calls this layer does not wrap (schedules, solver settings, state dumps, telemetry renders);
+    // owned by the multi handle: do not destroy it
+    if (!m) return ESIM_ERROR_INVALID_HANDLE;
+    if (!out || shard < 0 || shard >= (int)m->shard.size()) return ESIM_ERROR_INVALID_PARAMETER;
+    *out = m->shard[shard].get();
     return ESIM_SUCCESS;
 }
 

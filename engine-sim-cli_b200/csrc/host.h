@@ -4,6 +4,7 @@
 #include "esb_device.h"
 
 #include <cstdint>
+#include <stdexcept>
 #include <string>
 #include <vector>
 
@@ -18,6 +19,12 @@ struct LoadedPreset {
 // preset.cpp
 void parsePreset(const std::string &jsonText, LoadedPreset &out);
 void loadPresetFile(const std::string &path, LoadedPreset &out);
+// "*.json" -> preset, anything else -> engine script (SimulatorFactory.cpp:111-156 createPistonEngineSimulator)
+void loadEngineFile(const std::string &path, LoadedPreset &out);
+
+// mr_script.cpp — engine scripts without Piranha: script -> preset document (JSON text of PresetSerializer's schema)
+struct ScriptError : std::runtime_error { using std::runtime_error::runtime_error; };
+std::string compileScriptToPresetJson(const std::string &scriptPath, const std::vector<std::string> &searchPaths);
 
 // wav.cpp — 16-bit PCM RIFF reader/writer (replaces dr_wav, wav_loader.h:41-63)
 struct WavData {

@@ -279,6 +279,11 @@ void parsePreset(const std::string &text, LoadedPreset &out) {
     } else { p.gearCount = 0; p.currentGear = -1; }
 }
 
+void loadEngineFile(const std::string &path, LoadedPreset &out) {
+    if (path.size() >= 5 && path.compare(path.size() - 5, 5, ".json") == 0) { loadPresetFile(path, out); return; }
+    parsePreset(compileScriptToPresetJson(path, {}), out);
+}
+
 void loadPresetFile(const std::string &path, LoadedPreset &out) {
     std::ifstream f(path, std::ios::binary);
     if (!f) throw JsonError("Cannot open preset file: " + path);

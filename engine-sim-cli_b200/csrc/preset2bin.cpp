@@ -5,7 +5,7 @@
 int main(int argc, char **argv) {
     if (argc < 3) { std::fprintf(stderr, "usage: preset2bin <preset.json> <out.bin>\n"); return 2; }
     esb::LoadedPreset lp;
-    try { esb::loadPresetFile(argv[1], lp); } catch (const std::exception &e) { std::fprintf(stderr, "error: %s\n", e.what()); return 1; }
+    try { esb::loadEngineFile(argv[1], lp); } catch (const std::exception &e) { std::fprintf(stderr, "error: %s\n", e.what()); return 1; }
     FILE *f = std::fopen(argv[2], "wb");
     if (!f) return 1;
     std::fwrite(&lp.params, sizeof(lp.params), 1, f);

@@ -50,10 +50,12 @@ typedef struct EngineSimOpaque *EngineSimHandle;
 /* ISimulator::create(config) + SimulatorFactory defaults (EngineSimTypes.h:36-82). config may be NULL. */
 int32_t EngineSimCreate(const EngineSimConfig *config, EngineSimHandle *outHandle);
 /* SimulatorFactory::create(type, scriptPath, assetBasePath, ...) (SimulatorFactory.cpp:134-156):
- * a *.json preset is loaded directly (loadPresetSimulation, :95-109); impulse responses named by the
- * preset are read relative to assetBasePath (ScriptLoadHelpers.cpp:30-82).  *.mr scripts are compiled
- * to that preset document by the host-side front-end (engine_sim_cli_b200/mr_frontend.py, which the Python
- * API's load_script and the render CLI call); passed here directly they give ESIM_ERROR_SCRIPT_COMPILATION. */
+ * a *.json preset is loaded directly (loadPresetSimulation, :95-109), anything else is an engine script
+ * (createPistonEngineSimulator, :111-156) and is compiled by the library's own Piranha-free front-end
+ * (csrc/mr_script.cpp: the `.mr` subset the engine library uses and the __engine_sim__ built-in nodes; master /
+ * slave rods included, governed engines rejected).  Impulse responses named by the engine are read relative to
+ * assetBasePath (ScriptLoadHelpers.cpp:30-82).  A script that does not compile gives
+ * ESIM_ERROR_SCRIPT_COMPILATION with the front-end's message in EngineSimGetLastError. */
 int32_t EngineSimLoadScript(EngineSimHandle h, const char *scriptPath, const char *assetBasePath);
 /* Same, from memory: flat parameter blob (sizeof(EsbEngineParams)) and one mono s16 impulse response
  * used for every exhaust system. irSamples may be NULL (identity response). */
@@ -179,6 +181,36 @@ int32_t EsbFirRun(const float *dX, int64_t xStride, int64_t hist, const float *d
                   int32_t rows, int64_t count, float *dY, int64_t yStride, void *cudaStream);
 /* Pipe peak probes: runs a register-resident loop and returns achieved GFLOP/s (fp64: 0/1, fma: 0/1). */
 int32_t EsbProbePeak(int32_t fp64, int32_t fma, double *outGflops);
+/* ---- multi-device batch: the job's instances sharded over the GPUs of one box, no collective on the path ----
+ * (north_star: "each GPU writes its own WAVs and per-instance telemetry, gathered once to the host at the end"; SURVEY.md §8(b),(e)).
+ * Device d holds instancesPerDevice[d] consecutive instances of the job; instance i keeps its global index for noise seeds
+ * (config->seed + i), controls, PCM rows and WAV names, so the output does not depend on the sharding.  One host thread per device
+ * while rendering and writing.  shard = -1 addresses every device, 0..nDevices-1 one of them (one engine type per GPU). */
+typedef struct EsbMultiOpaque *EsbMultiHandle;
+int32_t EsbMultiCreate(int32_t nDevices, const int32_t *deviceIds, const int32_t *instancesPerDevice, const EngineSimConfig *config, EsbMultiHandle *out);
+int32_t EsbMultiDestroy(EsbMultiHandle m);
+const char *EsbMultiGetLastError(EsbMultiHandle m);
+int32_t EsbMultiGetShard(EsbMultiHandle m, int32_t shard, int32_t *outDevice, int32_t *outFirstInstance, int32_t *outInstances);
+/* The ordinary batch handle of one shard, for everything this layer does not wrap (owned by m: do not destroy it). */
+int32_t EsbMultiGetShardBatch(EsbMultiHandle m, int32_t shard, EsbBatchHandle *out);
+/* "*.json" preset or engine script, as EngineSimLoadScript */
+int32_t EsbMultiLoadEngineFile(EsbMultiHandle m, int32_t shard, const char *path, const char *assetBasePath);
+int32_t EsbMultiLoadParams(EsbMultiHandle m, int32_t shard, const EsbEngineParams *params);
+int32_t EsbMultiSetImpulseResponse(EsbMultiHandle m, int32_t shard, int32_t exhaust, const int16_t *samples, int32_t count, float volume, int32_t maxTaps);
+/* Controls of the job's instances [first, first + count), global indices */
+int32_t EsbMultiSetControls(EsbMultiHandle m, int32_t first, int32_t count, const EsbControls *controls);
+/* Largest per-instance sample count nSteps more steps produce on any shard (to size the pcm rows) */
+int32_t EsbMultiSamplesFor(EsbMultiHandle m, int32_t nSteps, int32_t *outMaxSamples);
+/* All devices advance nSteps at once.  pcm: host [nInstances][pcmStride] int16 in global order, or NULL (audio stays on the devices
+ * for EsbMultiWriteWavs); outSamples: [nDevices] samples per instance of each shard. */
+int32_t EsbMultiRender(EsbMultiHandle m, int32_t nSteps, int16_t *pcm, int64_t pcmStride, int32_t *outSamples);
+/* Every device writes the WAVs of its own instances (<prefix><global index>.wav), concurrently */
+int32_t EsbMultiWriteWavs(EsbMultiHandle m, const char *directory, const char *prefix);
+int32_t EsbMultiGetStats(EsbMultiHandle m, int32_t instance, EngineSimStats *out);
+
+/* Compiles an engine script to the preset document (JSON text, PresetSerializer.cpp:35-385 schema) without loading it.
+ * outJson may be NULL to query the length; the text is NUL-terminated when it fits. */
+int32_t EsbCompileScript(const char *scriptPath, char *outJson, int64_t capacity, int64_t *outLength);
 /* Sizes of the binary contracts of this build: sizeof(EsbEngineParams) (the parameter blob of EsbBatchLoadParams /
  * EngineSimLoadParams) and the number of fields of the state block EsbBatchGetState returns. */
 int32_t EsbGetLayout(int32_t *outParamsBytes, int32_t *outStateFields);

@@ -60,7 +60,7 @@ def main():
     csrc = os.path.join(ROOT, "engine-sim-cli_b200", "csrc")
     exe = os.path.join(build, "preset2bin")
     subprocess.run(["g++", "-O2", "-std=c++17", "-I" + os.path.join(ROOT, "include"), "-I" + csrc,
-                    os.path.join(csrc, "preset2bin.cpp"), os.path.join(csrc, "preset.cpp"), os.path.join(csrc, "wav.cpp"),
+                    os.path.join(csrc, "preset2bin.cpp"), os.path.join(csrc, "preset.cpp"), os.path.join(csrc, "mr_script.cpp"), os.path.join(csrc, "wav.cpp"),
                     "-o", exe], check=True)
     for name, rel in PRESETS.items():
         out = os.path.join(HERE, name + ".params.bin")
@@ -69,6 +69,8 @@ def main():
         ir = read_wav_mono16(os.path.join(REF, "es", irs[0]))
         np.save(os.path.join(HERE, name + ".ir.npy"), ir)
         print(name, r.stdout.splitlines()[0], "ir", irs[0], len(ir))
+    # the self-written twin of tests/golden/mr_mini, straight from the script through the library's own front-end (mr_script.cpp)
+    subprocess.run([exe, os.path.join(HERE, "mr_mini", "twin.mr"), os.path.join(HERE, "mini_twin.params.bin")], check=True, capture_output=True, text=True)
     # gm_ls with evacuated chambers at the start: gas exchanges with an empty cell, i.e. the exact-arithmetic path of the kernel
     import json as _json
     doc = _json.load(open(os.path.join(REF, PRESETS["gm_ls"])))

@@ -49,7 +49,7 @@ def _preset2bin():
     csrc = os.path.join(ROOT, "engine-sim-cli_b200", "csrc")
     os.makedirs(os.path.dirname(exe), exist_ok=True)
     subprocess.run(["g++", "-O2", "-std=c++17", "-I" + os.path.join(ROOT, "include"), "-I" + csrc, os.path.join(csrc, "preset2bin.cpp"),
-                    os.path.join(csrc, "preset.cpp"), os.path.join(csrc, "wav.cpp"), "-o", exe], check=True)
+                    os.path.join(csrc, "preset.cpp"), os.path.join(csrc, "mr_script.cpp"), os.path.join(csrc, "wav.cpp"), "-o", exe], check=True)
     return exe
 
 

@@ -146,7 +146,7 @@ def test_compiled_scripts_load_into_the_committed_blobs(tmp_path):
     csrc = os.path.join(ROOT, "engine-sim-cli_b200", "csrc")
     exe = str(tmp_path / "preset2bin")
     subprocess.run(["g++", "-O2", "-std=c++17", "-I" + os.path.join(ROOT, "include"), "-I" + csrc, os.path.join(csrc, "preset2bin.cpp"),
-                    os.path.join(csrc, "preset.cpp"), os.path.join(csrc, "wav.cpp"), "-o", exe], check=True)
+                    os.path.join(csrc, "preset.cpp"), os.path.join(csrc, "mr_script.cpp"), os.path.join(csrc, "wav.cpp"), "-o", exe], check=True)
     man = json.load(open(os.path.join(ROOT, "tests", "golden", "mr_manifest.json")))
     for name, info in man.items():
         doc = m.compile_script(os.path.join(REF, info["script"]))
@@ -157,3 +157,72 @@ def test_compiled_scripts_load_into_the_committed_blobs(tmp_path):
         assert out.read_bytes() == open(os.path.join(ROOT, "tests", "golden", name + ".params.bin"), "rb").read(), name
     hay = m.compile_script(os.path.join(REF, man["hayabusa_i4"]["script"]))["engine"]
     assert [c["exhaustSystemIndex"] for b in hay["cylinderBanks"] for c in b["cylinders"]] == [0, 1, 0, 1]
+
+
+# ---- the library's own front-end (csrc/mr_script.cpp, what EngineSimLoadScript("*.mr") runs): no Python in the loop ----
+def _compile_c(path):
+    import engine_sim_cli_b200 as esb
+    return esb.compile_script(path)
+
+
+def test_library_front_end_on_the_mini_library(tmp_path):
+    """EsbCompileScript on the self-contained mini library equals the Python twin, and its errors carry file and reason."""
+    import engine_sim_cli_b200 as esb
+    m = _mr()
+    src = os.path.join(MINI, "twin.mr")          # a complete (self-written) engine on the mini library
+    doc = _compile_c(src)
+    out = []
+    _compare(doc, m.compile_script(src), "", out)
+    assert out == []
+    e = doc["engine"]
+    assert (e["name"], e["cylinderCount"], e["exhaustSystemCount"]) == ("Mini twin 650", 2, 1)
+    assert e["ignitionModule"]["firingOrder"] == pytest.approx([0.0, 2 * 3.14159265359])
+    assert e["exhaustSystems"][0]["impulseResponseFilename"] == "sound-library/test/tiny_ir.wav"
+    (tmp_path / "noengine.mr").write_text('import "engine_sim.mr"\npublic node main { output x: 1; }\n')
+    import shutil
+    shutil.copy(os.path.join(MINI, "engine_sim.mr"), tmp_path / "engine_sim.mr")
+    with pytest.raises(esb.EngineSimError, match="never calls set_engine") as e:
+        _compile_c(str(tmp_path / "noengine.mr"))
+    assert e.value.code == -6                                    # ESIM_ERROR_SCRIPT_COMPILATION
+    (tmp_path / "syntax.mr").write_text("public node main { input a [float: 1; }")
+    with pytest.raises(esb.EngineSimError, match="syntax.mr:1"):
+        _compile_c(str(tmp_path / "syntax.mr"))
+    with pytest.raises(esb.EngineSimError, match="no such script"):
+        _compile_c(str(tmp_path / "missing.mr"))
+
+
+@needs_ref
+@pytest.mark.parametrize("script,fixture", [("engines/atg-video-2/07_gm_ls.mr", "gm_ls"), ("engines/atg-video-1/01_honda_trx520.mr", "01_honda_trx520"),
+                                            ("engines/atg-video-2/01_subaru_ej25_eh.mr", "01_subaru_ej25_eh")])
+def test_library_front_end_reproduces_the_reference_pairs(script, fixture):
+    """The same pin as the Python twin's: the reference's own script <-> preset fixture pairs, every numeric field to 1e-9."""
+    doc = _compile_c(os.path.join(REF, "es", script))
+    ref = json.load(open(os.path.join(REF, "test", "fixtures", fixture + ".preset.json")))
+    diffs = []
+    _compare(doc["engine"], {k: v for k, v in ref["engine"].items() if k not in ("exhaustSystems",)}, "engine", diffs)
+    for got, want in zip(doc["engine"]["exhaustSystems"], ref["engine"]["exhaustSystems"]):
+        _compare(got, {k: v for k, v in want.items() if k != "impulseResponseFilename"}, "exhaust", diffs)
+        assert want["impulseResponseFilename"].endswith(got["impulseResponseFilename"])
+    assert diffs == []
+
+
+@needs_ref
+def test_library_front_end_equals_the_python_twin_on_every_script():
+    import glob
+    import engine_sim_cli_b200 as esb
+    m = _mr()
+    n = 0
+    for p in sorted(glob.glob(os.path.join(REF, "es", "engines", "*", "*.mr"))) + [os.path.join(REF, "es", "main.mr")]:
+        if os.path.basename(p) in ("radial.mr", "M156.mr"):
+            continue
+        try:
+            want = m.compile_script(p)
+        except m.MrError as e:
+            with pytest.raises(esb.EngineSimError, match="governor"):
+                _compile_c(p)
+            continue
+        out = []
+        _compare(_compile_c(p), want, "", out)
+        assert out == [], (p, out[:4])
+        n += 1
+    assert n >= 20
