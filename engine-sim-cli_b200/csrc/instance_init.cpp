@@ -172,6 +172,7 @@ void initialStateColumn(const EsbDeviceParams &D, std::vector<double> &col) {
     for (int k = 0; k < P.exhaustSystemCount; ++k)
         putCell(col, ESB_GF_COLLECTOR + 8 * k, 1, makeCell(kAtm, P.exhaust[k].collectorCrossSectionArea * P.exhaust[k].length, kT25C, 0, 1, 0));
     col[ESB_GF_THROTTLE_PLATE] = 1.0;
+    col[ESB_GF_VEH_INV_INERTIA] = D.invVehInertia;
     // Crankshaft::getCycleAngle at theta = 0
     {
         double r = std::fmod(-(0.0 - P.tdc), 4.0 * kPi);

@@ -45,6 +45,13 @@ void orc_sim_set_controls(void *h, double throttle, int ignition, int starter, i
     c.dynoSpeed = dynoSpeed; c.dynoMaxTorque = dynoMaxTorque;
 }
 
+void orc_sim_set_drivetrain(void *h, double clutchPressure, double brake) {
+    Controls &c = ((Simulator *)h)->engine.ctl;
+    c.clutchPressure = clutchPressure; c.brake = brake;
+}
+void orc_sim_change_gear(void *h, int gear) { ((Simulator *)h)->engine.changeGear(gear); }
+double orc_sim_vehicle_inv_inertia(void *h) { const Engine &e = ((Simulator *)h)->engine; return e.bodies[e.nb - 1].invI; }
+
 #define ORC_TELEMETRY_STRIDE 8
 static void telemetry(const Simulator &s, double *t) {
     const Engine &e = s.engine;

@@ -83,6 +83,8 @@ struct Controls {
     double dynoSpeed = 0;      // rad/s (BridgeSimulator.cpp:328)
     double dynoMaxTorque = 0;  // N m
     double clutchPressure = 0, brake = 0;
+    int gear = -1;             // engine-sim convention: -1 neutral, 0.. forward gears (GearConventions.h); Transmission::changeGear
+    double dynoKs = 10.0, dynoKd = 1.0; // Dynamometer::m_ks / m_kd (RealEngineAudioSpike.cpp:163-164): carried, see ASSUMPTIONS.md #3a
 };
 
 struct SolverConfig {
@@ -124,6 +126,7 @@ struct Engine {
 
     void initialize(const EsbEngineParams &p, double simFreq, int fluidSteps, uint64_t seed);
     void step();
+    void changeGear(int newGear);   // Transmission::changeGear
     double rpm() const { return -bodies[0].w * (30.0 / kPi); }
     double cycleAngle() const;
     double chamberVolume(int i) const;

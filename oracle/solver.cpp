@@ -39,13 +39,13 @@ void Engine::buildRows() {
     // ClutchConstraint crank <-> vehicle mass (BridgeSimulator.cpp:150-157)
     {
         Row r; r.b0 = 0; r.b1 = vehIdx; r.J0[2] = -1; r.J1[2] = 1; r.rhs = 0;
-        const double lim = (P.currentGear >= 0) ? P.maxClutchTorque * ctl.clutchPressure * dt : 0.0;
+        const double lim = (ctl.gear >= 0) ? P.maxClutchTorque * ctl.clutchPressure * dt : 0.0;
         r.lo = -lim; r.hi = lim; rowClutch = (int)rows.size(); rows.push_back(r);
     }
     // VehicleDragConstraint + BrakeConstraint on the vehicle mass
     {
         double ratio = 0;
-        if (P.currentGear >= 0 && P.currentGear < P.gearCount) ratio = P.tireRadius / (P.diffRatio * P.gearRatios[P.currentGear]);
+        if (ctl.gear >= 0 && ctl.gear < P.gearCount) ratio = P.tireRadius / (P.diffRatio * P.gearRatios[ctl.gear]);
         const double v = std::fabs(bodies[vehIdx].w) * ratio;
         const double F = 0.5 * 1.225 * P.dragCoefficient * P.crossSectionArea * v * v + P.rollingResistance;
         Row r; r.b0 = vehIdx; r.J0[2] = 1; r.rhs = 0; r.lo = -F * ratio * dt; r.hi = F * ratio * dt; rows.push_back(r);

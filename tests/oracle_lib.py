@@ -34,6 +34,10 @@ def lib():
         L.orc_sim_set_fir_mode.argtypes = [C.c_void_p, C.c_int]
         L.orc_sim_set_solver.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double]
         L.orc_sim_set_sample_rate.argtypes = [C.c_void_p, C.c_int]
+        L.orc_sim_set_drivetrain.argtypes = [C.c_void_p, C.c_double, C.c_double]
+        L.orc_sim_change_gear.argtypes = [C.c_void_p, C.c_int]
+        L.orc_sim_vehicle_inv_inertia.argtypes = [C.c_void_p]
+        L.orc_sim_vehicle_inv_inertia.restype = C.c_double
         L.orc_sim_set_controls.argtypes = [C.c_void_p, C.c_double, C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double]
         L.orc_sim_get_telemetry.argtypes = [C.c_void_p, C.c_void_p]
         L.orc_sim_get_state.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
@@ -84,6 +88,16 @@ class OracleSim:
     def set_sample_rate(self, rate):
         lib().orc_sim_set_sample_rate(self.h, int(rate))
         self.sample_rate = int(rate)
+
+    def set_drivetrain(self, clutch_pressure=0.0, brake=0.0):
+        lib().orc_sim_set_drivetrain(self.h, float(clutch_pressure), float(brake))
+
+    def change_gear(self, gear):
+        """Transmission::changeGear, engine-sim convention (-1 neutral)."""
+        lib().orc_sim_change_gear(self.h, int(gear))
+
+    def vehicle_inv_inertia(self):
+        return lib().orc_sim_vehicle_inv_inertia(self.h)
 
     def set_fir_mode(self, mode):
         lib().orc_sim_set_fir_mode(self.h, int(mode))
