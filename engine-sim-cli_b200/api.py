@@ -102,7 +102,7 @@ def lib():
             "EsbBatchSetAudioParams": [vp, flt, flt, flt, flt, flt], "EsbBatchSetSolver": [vp, i32, dbl, dbl], "EsbBatchSetSineMode": [vp, i32],
             "EsbBatchSetControls": [vp, i32, i32, vp], "EsbBatchSetGear": [vp, i32, i32, vp], "EsbBatchGetControls": [vp, i32, vp], "EsbBatchSetSchedule": [vp, i32, vp, vp, vp], "EsbBatchReset": [vp],
             "EsbBatchRender": [vp, i32, vp, vp, i64, C.POINTER(i32), vp, i32, i32], "EsbBatchTelemetrySamplesFor": [vp, i32, i32, C.POINTER(i32)],
-            "EsbBatchGetStepCount": [vp, C.POINTER(i64)], "EsbBatchSamplesFor": [vp, i32, C.POINTER(i32)],
+            "EsbBatchGetStepCount": [vp, C.POINTER(i64)], "EsbBatchGetSimulationFrequency": [vp, C.POINTER(dbl)], "EsbBatchSamplesFor": [vp, i32, C.POINTER(i32)],
             "EsbBatchGetDevicePcm": [vp, C.POINTER(vp), C.POINTER(i64), C.POINTER(i32)], "EsbBatchGetState": [vp, vp, C.POINTER(i32)],
             "EsbBatchGetLastStream": [vp, vp, i32, C.POINTER(i32)], "EsbBatchGetStats": [vp, i32, vp], "EsbBatchWriteWavs": [vp, C.c_char_p, C.c_char_p],
             "EsbBatchSetLaunchConfig": [vp, i32, i32], "EsbBatchGetLaunchCounts": [vp, vp],
@@ -297,6 +297,16 @@ class BatchSimulator:
         if tel is not None:
             tel = tel[:k]
         return (pcm[:, :n] if pcm is not None else None), (pcmf[:, :n] if pcmf is not None else None), tel
+
+    def simulation_frequency(self):
+        """The physics rate of the loaded engine (the config's value, else the engine's own)."""
+        out = C.c_double()
+        self._check(lib().EsbBatchGetSimulationFrequency(self.h, C.byref(out)))
+        return out.value
+
+    @staticmethod
+    def controls_bytes_per_instance():
+        return C.sizeof(EsbControls)
 
     def step_count(self):
         out = C.c_int64()

@@ -151,6 +151,13 @@ int32_t EsbBatchTelemetrySamplesFor(EsbBatchHandle h, int32_t nSteps, int32_t te
     *out = (int32_t)h->b.telemetrySamplesFor(nSteps, telEvery);
     return ESIM_SUCCESS;
 }
+int32_t EsbBatchGetSimulationFrequency(EsbBatchHandle h, double *out) {
+    if (!h) return ESIM_ERROR_INVALID_HANDLE;
+    if (!out) return ESIM_ERROR_INVALID_PARAMETER;
+    if (!h->b.loaded) { h->b.lastError = "no engine loaded"; return ESIM_ERROR_NOT_INITIALIZED; }
+    *out = h->b.simFreq;
+    return ESIM_SUCCESS;
+}
 int32_t EsbBatchGetStepCount(EsbBatchHandle h, int64_t *out) {
     if (!h) return ESIM_ERROR_INVALID_HANDLE;
     if (!out) return ESIM_ERROR_INVALID_PARAMETER;

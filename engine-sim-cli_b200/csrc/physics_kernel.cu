@@ -10,17 +10,16 @@
 
 namespace esbk {
 
-// MINB = resident blocks of 64 threads the compiler must make room for: 4 -> up to 255 registers per
-// thread (8 warps / SM), 7 -> 146, 8 -> 128 (16 warps / SM).  With instPerWarp < 32 / G the warps are
-// deliberately left part-empty: a batch too small to fill the machine is latency-bound, and more warps
-// hide more of the FP64 dependency latency than full warps do.
-template <int G, int MINB>
-__global__ void __launch_bounds__(256, (MINB >= 7 ? 2 : 1)) esb_physics_kernel(RunArgs a, int instPerWarp) {
+// SLAVES: engines with master / slave connecting rods (radial engines) take the general form of the rod-journal rows.
+template <int G, bool SLAVES>
+__global__ void __launch_bounds__(256, 1) esb_physics_kernel(RunArgs a, int instPerWarp) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int laneInWarp = threadIdx.x & 31;
     const int slot = laneInWarp / G;
     // No thread leaves early (every thread of the block takes part in the lockstep barriers): lane groups
     // without an instance of their own shadow the last instance and store nothing.
+    // With instPerWarp < 32 / G the warps are deliberately left part-empty: a batch too small to fill the machine is
+    // latency-bound, and more warps hide more of the FP64 dependency latency than full warps do.
     int inst = warp * instPerWarp + slot;
     const bool live = slot < instPerWarp && inst < a.nInst;
     if (!live) inst = a.nInst - 1;
@@ -38,7 +37,7 @@ __global__ void __launch_bounds__(256, (MINB >= 7 ? 2 : 1)) esb_physics_kernel(R
     g.clkOn = blockIdx.x == 0 && threadIdx.x == 0;
     g.clkLast = clock64();
 #endif
-    runInstance<G>(a, inst, live, g, view);
+    runInstance<G, SLAVES>(a, inst, live, g, view);
 }
 
 } // namespace esbk
@@ -57,17 +56,17 @@ cudaError_t esbLaunchFastArCheck(int op, int n, const double *a, const double *b
     return cudaGetLastError();
 }
 
-template <int G, int MINB>
+template <int G, bool SLAVES>
 static cudaError_t launchKernel(const esbk::RunArgs &a, int grid, int blockThreads, int instPerWarp, size_t smem, cudaStream_t stream) {
     // per (function, device): set before every launch, a process may drive several devices
-    cudaError_t e = cudaFuncSetAttribute(esbk::esb_physics_kernel<G, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(esbk::esb_physics_kernel<G, SLAVES>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    esbk::esb_physics_kernel<G, MINB><<<grid, blockThreads, smem, stream>>>(a, instPerWarp);
+    esbk::esb_physics_kernel<G, SLAVES><<<grid, blockThreads, smem, stream>>>(a, instPerWarp);
     return cudaGetLastError();
 }
 
 template <int G>
-static cudaError_t launchG(const esbk::RunArgs &a, const EsbDeviceParams &hostD, int blockThreads, int instPerWarp, int variant, cudaStream_t stream) {
+static cudaError_t launchG(const esbk::RunArgs &a, const EsbDeviceParams &hostD, int blockThreads, int instPerWarp, cudaStream_t stream) {
     const int full = 32 / G;
     if (instPerWarp <= 0 || instPerWarp > full) instPerWarp = full;
     const long long warps = ((long long)a.nInst + instPerWarp - 1) / instPerWarp;
@@ -75,19 +74,24 @@ static cudaError_t launchG(const esbk::RunArgs &a, const EsbDeviceParams &hostD,
     const int grid = (int)((warps + wpb - 1) / wpb);
     const esbk::GasSmemLayout L = esbk::gasSmemLayout(hostD.gas, hostD.P.cylinderCount, hostD.P.intakeCount, hostD.fluidSteps, blockThreads / G);
     if (L.total > 227u * 1024u) return cudaErrorInvalidConfiguration;
-    if (G == 8 && variant == 1) return launchKernel<G, (G == 8 ? 7 : 4)>(a, grid, blockThreads, instPerWarp, L.total, stream);
-    if (G == 8 && variant == 2) return launchKernel<G, (G == 8 ? 8 : 4)>(a, grid, blockThreads, instPerWarp, L.total, stream);
-    return launchKernel<G, 4>(a, grid, blockThreads, instPerWarp, L.total, stream);
+    bool slaves = false;
+    for (int i = 0; i < hostD.P.cylinderCount; ++i) slaves = slaves || hostD.P.cyl[i].masterCylinder >= 0;
+    if (slaves) {
+        // master / slave rods exist in the radial engines (5, 7, 9 cylinders): built for 8 and 16 lanes
+        if constexpr (G == 8 || G == 16) return launchKernel<G, true>(a, grid, blockThreads, instPerWarp, L.total, stream);
+        else return cudaErrorNotSupported;
+    }
+    return launchKernel<G, false>(a, grid, blockThreads, instPerWarp, L.total, stream);
 }
 
-cudaError_t esbLaunchPhysics(const esbk::RunArgs &a, const EsbDeviceParams &hostD, int blockThreads, int instPerWarp, int variant, cudaStream_t stream) {
+cudaError_t esbLaunchPhysics(const esbk::RunArgs &a, const EsbDeviceParams &hostD, int blockThreads, int instPerWarp, int /*variant*/, cudaStream_t stream) {
     if (blockThreads % 32 != 0 || blockThreads < 32 || blockThreads > 256) return cudaErrorInvalidValue;
     switch (hostD.lanesPerInstance) {
-    case 1: return launchG<1>(a, hostD, blockThreads, instPerWarp, variant, stream);
-    case 2: return launchG<2>(a, hostD, blockThreads, instPerWarp, variant, stream);
-    case 4: return launchG<4>(a, hostD, blockThreads, instPerWarp, variant, stream);
-    case 8: return launchG<8>(a, hostD, blockThreads, instPerWarp, variant, stream);
-    case 16: return launchG<16>(a, hostD, blockThreads, instPerWarp, variant, stream);
+    case 1: return launchG<1>(a, hostD, blockThreads, instPerWarp, stream);
+    case 2: return launchG<2>(a, hostD, blockThreads, instPerWarp, stream);
+    case 4: return launchG<4>(a, hostD, blockThreads, instPerWarp, stream);
+    case 8: return launchG<8>(a, hostD, blockThreads, instPerWarp, stream);
+    case 16: return launchG<16>(a, hostD, blockThreads, instPerWarp, stream);
     default: return cudaErrorInvalidValue;
     }
 }

@@ -114,7 +114,7 @@ ESB_DEV double scheduleValue(const long long *keyStep, const double *keyVal, int
     return v0 + (v1 - v0) * a;
 }
 
-template <int G>
+template <int G, bool SLAVES>
 ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &g, const GasView &v) {
     const EsbDeviceParams *D = a.D;
     const size_t n = (size_t)a.nInst;
@@ -188,7 +188,7 @@ ESB_DEV void runInstance(const RunArgs &a, int inst, bool live, const Group<G> &
         double out[ESB_MAX_EXHAUST];
         // exhaust-flow total: on telemetry steps, and on the last step of every launch so that the stored statistic
         // (EsbBatchGetStats().exhaustFlow, BridgeSimulator::getStats) is current whatever the telemetry interval
-        const double exhaustFlow = simulateStep<G>(s, k, D, ctl, g, v, seed, delayed, out, sample || step + 1 == a.nSteps);
+        const double exhaustFlow = simulateStep<G, SLAVES>(s, k, D, ctl, g, v, seed, delayed, out, sample || step + 1 == a.nSteps);
         if (k.active) {
             if (live) ring[(size_t)s.delayPos * ringStride] = exhaustFlow;
             s.delayPos = (s.delayPos + 1 == k.delayLen) ? 0 : s.delayPos + 1;

@@ -173,6 +173,8 @@ int32_t EsbBatchRender(EsbBatchHandle b, int32_t nSteps, int16_t *pcm, float *pc
 int32_t EsbBatchTelemetrySamplesFor(EsbBatchHandle b, int32_t nSteps, int32_t telemetryEvery, int32_t *outSamples);
 /* Steps simulated since the last reset (EsbBatchReset, EsbBatchSetSolver and a reload restart it). */
 int32_t EsbBatchGetStepCount(EsbBatchHandle b, int64_t *outSteps);
+/* Physics rate of the loaded engine: the config's simulationFrequency when given, else the engine's own (SimulatorFactory.cpp:63-64) */
+int32_t EsbBatchGetSimulationFrequency(EsbBatchHandle b, double *outHz);
 /* Number of samples nSteps more steps will produce (host arithmetic only). */
 int32_t EsbBatchSamplesFor(EsbBatchHandle b, int32_t nSteps, int32_t *outSamples);
 /* Device pointers of the last render (int16 [nInstances][stride]) for zero-copy consumers. */

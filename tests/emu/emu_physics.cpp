@@ -24,6 +24,8 @@ double *emuSlots(EmuShared *s) { return s->slots; }
 } // namespace esbk
 
 template <int G> static void runGroup(const esbk::RunArgs &a, int inst) {
+    bool slaves = false;
+    for (int i = 0; i < a.D->P.cylinderCount; ++i) slaves = slaves || a.D->P.cyl[i].masterCylinder >= 0;
     esbk::EmuShared sh(G);
     // the block's "shared memory": same layout as on the device, one lane group
     const EsbGasNet &gn = a.D->gas;
@@ -36,7 +38,8 @@ template <int G> static void runGroup(const esbk::RunArgs &a, int inst) {
     for (int lane = 0; lane < G; ++lane)
         th.emplace_back([&, lane] {
             esbk::Group<G> g; g.lane = lane; g.mask = 0; g.sh = &sh;
-            esbk::runInstance<G>(a, inst, true, g, view);
+            if (slaves) esbk::runInstance<G, true>(a, inst, true, g, view);
+            else esbk::runInstance<G, false>(a, inst, true, g, view);
         });
     for (auto &t : th) t.join();
 }
