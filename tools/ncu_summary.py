@@ -1,5 +1,5 @@
 """Summarise an .ncu-rep (one kernel launch) into a small JSON for profiles/.  Usage:
-python tools/ncu_summary.py gpurun_out/prof.ncu-rep profiles/name.json"""
+python tools/ncu_summary.py gpurun_out/prof.ncu-rep profiles/name.json [steps_in_launch instances]"""
 import csv
 import json
 import subprocess
@@ -52,6 +52,8 @@ def main():
     r, w = to_bytes(d.get("dram_read")), to_bytes(d.get("dram_write"))
     if r is not None and w is not None:
         d["dram_bytes_per_launch"] = r + w
+    if len(sys.argv) > 4:
+        d["steps_in_launch"], d["instances"] = int(sys.argv[3]), int(sys.argv[4])
     json.dump(d, open(out, "w"), indent=1)
     print(json.dumps(d, indent=1)[:1500])
 
