@@ -22,18 +22,21 @@ def disassemble(so):
 
 
 def functions(txt):
+    """[(name, [instructions])] of the 8-lane kernel: its body, then every out-of-line device function (split at their labels)."""
     txt = txt.split("\n")
-    start = [i for i, l in enumerate(txt) if l.startswith(".text._ZN4esbk18esb_physics_kernelILi8ELi4E")][0]
+    start = [i for i, l in enumerate(txt) if l.startswith(".text._ZN4esbk18esb_physics_kernelILi8ELb0E")][0]
     end = [i for i, l in enumerate(txt) if l.startswith(".text.") and i > start][0]
-    seg, cur = [], []
+    seg, cur, name = [], [], "kernel body"
     for l in txt[start:end]:
+        m = re.match(r"^\$.*?4esbk\d+([A-Za-z_0-9]+?)E[PdRKiv]", l) or re.match(r"^\$__internal_\d+_\$(\w+):", l)
+        if m:
+            seg.append((name, cur))
+            cur, name = [], m.group(1)
+            continue
         m = re.match(r"\s*/\*([0-9a-f]{4,6})\*/\s+(.*?);", l)
         if m:
             cur.append(m.group(2).strip())
-            if m.group(2).startswith("RET."):
-                seg.append(cur)
-                cur = []
-    seg.append(cur)
+    seg.append((name, cur))
     return seg
 
 
@@ -50,9 +53,12 @@ def regs(tok, wide):
     return out
 
 
-def model(fn):
+def model(fn, dataflow=False):
+    """In-order issue time of the function; dataflow=True: the dependency-only bound (every instruction issues as soon as its
+    operands are ready: what a perfect schedule of the same instructions could reach)."""
     ready = {}
     t = 0
+    longest = 0
     for ins in fn:
         parts = ins.split(None, 1)
         pred = []
@@ -75,21 +81,23 @@ def model(fn):
         if base == "DSETP":
             lat = 10
         issue = 2 if base in FP64 else 1
-        start = max([t] + [ready.get(r, 0) for r in src])
+        start = max(([0] if dataflow else [t]) + [ready.get(r, 0) for r in src])
         for r in dst:
             ready[r] = start + lat
+        longest = max(longest, start + lat)
         t = start + issue
-    return t
+    return longest if dataflow else t
 
 
 def main():
     arg = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "engine-sim-cli_b200", "libenginesim_b200.so")
     txt = open(arg).read() if arg.endswith(".sass") else disassemble(arg)
-    for k, fn in enumerate(functions(txt)):
-        if len(fn) >= 300 and k > 0:
+    for name, fn in functions(txt):
+        if len(fn) >= 300 and name != "kernel body":
             cyc = model(fn)
             nfp = sum(1 for i in fn if (i.split()[1] if i.startswith("@") else i.split()[0]).split(".")[0] in FP64)
-            print(f"function {k}: {len(fn)} instr, {nfp} FP64 -> {cyc} cycles alone ({cyc / len(fn):.2f} per instr; issue-bound floor {len(fn) + nfp})")
+            print(f"{name}: {len(fn)} instr, {nfp} FP64 -> {cyc} cycles alone ({cyc / len(fn):.2f} per instr; issue-bound floor {len(fn) + nfp}; "
+                  f"dependency-only bound {model(fn, True)})")
 
 
 if __name__ == "__main__":
