@@ -197,6 +197,25 @@ class BatchSession:
         self.time_s += self.tick_dt
         return pcm
 
+    def run_replay_on_device(self, trace, seconds=None, auto_start=True, want_pcm=True):
+        """The same replay as run_replay, but as ONE render call: the per-tick control code runs inside the physics launches
+        (BatchSimulator.set_session / EsbBatchSetSession).  Returns (pcm, phase history, rpm history) like run_replay."""
+        end = float(trace["time"][-1]) if seconds is None else seconds
+        n_ticks = int(math.ceil(end / self.tick_dt))
+        inputs = np.zeros((n_ticks, 4))
+        t = 0.0
+        for k in range(n_ticks):
+            t += self.tick_dt
+            i = replay_sample_index(trace["time"], t)
+            inputs[k] = (trace["throttle"][i], 1.0, 1.0 if (auto_start and k == 0) else 0.0, trace["rpm"][i] if "rpm" in trace else -1.0)
+        self.b.set_session(inputs, self.steps_per_tick)
+        pcm, _, _ = self.b.render(n_ticks * self.steps_per_tick, want_pcm=want_pcm)
+        phases, rpms = self.b.session_log()
+        self.b.set_session(None, 0)
+        self.phase, self.rpm = phases[-1].copy(), rpms[-1].copy()
+        self.time_s += n_ticks * self.tick_dt
+        return pcm, phases, rpms
+
     def run_replay(self, trace, seconds=None, auto_start=True, want_pcm=True):
         """Replays one trace for every instance (sample-and-hold); returns (pcm [n, samples] or None, phase history [ticks, n],
         rpm history [ticks, n])."""

@@ -70,7 +70,7 @@ void Batch::release() {
     if (device >= 0) cudaSetDevice(device);
     auto fr = [](auto *&p) { if (p) { cudaFree(p); p = nullptr; } };
     fr(dD); fr(dS); fr(dCtl); fr(dKeyStep); fr(dKeyThr); fr(dKeyDyno); fr(dStream); fr(dChanState); fr(dChanLast); fr(dInstState);
-    fr(dX); fr(dHr); fr(dY); fr(dPcm); fr(dPcmFloat); fr(dTel); fr(dSinePhase);
+    fr(dX); fr(dHr); fr(dY); fr(dPcm); fr(dPcmFloat); fr(dTel); fr(dSinePhase); fr(dTickInputs); fr(dTickLog);
     for (auto &t : timed) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
     for (auto e : eventPool) cudaEventDestroy(e);
     timed.clear(); eventPool.clear();
@@ -249,6 +249,7 @@ int Batch::reset() {
     streamCapSteps = stepsPerLaunch;
     lastStreamSteps = 0;
     stepCount = 0;
+    sessionTicks = 0; sessionStepsPerTick = 0;   // a device-side session belongs to the run it was set in
     samplesProduced = 0;
     clock.inputWriteOffset = 0; clock.lastInputSampleOffset = 0; clock.writeIndex = 0;
     clock.samplesPerStep = (double)cfg.sampleRate / simFreq;
@@ -398,6 +399,37 @@ int Batch::setSchedule(int nk, const int64_t *keyStep, const double *thr, const 
     return ESIM_SUCCESS;
 }
 
+int Batch::setSession(int nTicks, int stepsPerTick, const double *inputs, int stride, double dynoMaxTorque) {
+    if (!loaded) { lastError = "no engine loaded"; return ESIM_ERROR_NOT_INITIALIZED; }
+    ESB_CUDA(cudaSetDevice(device));
+    ESB_CUDA(cudaStreamSynchronize(stream));
+    if (dTickInputs) { cudaFree(dTickInputs); dTickInputs = nullptr; }
+    if (dTickLog) { cudaFree(dTickLog); dTickLog = nullptr; }
+    sessionTicks = 0; sessionStepsPerTick = 0;
+    if (nTicks <= 0) return ESIM_SUCCESS;   // session off: controls and schedules apply again
+    if (stepsPerTick <= 0 || !inputs || (stride != 1 && stride != nInst)) { lastError = "session needs stepsPerTick > 0, inputs and a stride of 1 or nInstances"; return ESIM_ERROR_INVALID_PARAMETER; }
+    const size_t inBytes = (size_t)nTicks * 4 * stride * sizeof(double), logBytes = (size_t)nTicks * 2 * nInst * sizeof(double);
+    ESB_CUDA(cudaMalloc(&dTickInputs, inBytes));
+    ESB_CUDA(cudaMalloc(&dTickLog, logBytes));
+    ESB_CUDA(cudaMemcpy(dTickInputs, inputs, inBytes, cudaMemcpyHostToDevice));
+    ESB_CUDA(cudaMemset(dTickLog, 0, logBytes));
+    // the controller of every instance starts as a fresh CrankingController on a stopped engine
+    ESB_CUDA(cudaMemset(dS + (size_t)ESB_GF_SESSION * nInst, 0, (size_t)7 * nInst * sizeof(double)));
+    sessionTicks = nTicks; sessionStepsPerTick = stepsPerTick; sessionStride = stride; sessionBase = stepCount; sessionDynoMaxTorque = dynoMaxTorque;
+    return ESIM_SUCCESS;
+}
+int Batch::getSessionLog(double *out, int maxTicks, int *outTicks) {
+    const long long done = sessionStepsPerTick > 0 ? std::min<long long>((stepCount - sessionBase) / sessionStepsPerTick, sessionTicks) : 0;
+    const int k = (int)std::min<long long>(done, maxTicks);
+    if (outTicks) *outTicks = k;
+    if (out && k > 0) {
+        ESB_CUDA(cudaSetDevice(device));
+        ESB_CUDA(cudaStreamSynchronize(stream));
+        ESB_CUDA(cudaMemcpy(out, dTickLog, (size_t)k * 2 * nInst * sizeof(double), cudaMemcpyDeviceToHost));
+    }
+    return ESIM_SUCCESS;
+}
+
 int Batch::setLaunchConfig(int blockThreads_, int stepsPerLaunch_) {
     if (blockThreads_ > 0) {
         if (blockThreads_ % 32 != 0 || blockThreads_ > 256) { lastError = "blockThreads must be a multiple of 32, at most 256"; return ESIM_ERROR_INVALID_PARAMETER; }
@@ -437,6 +469,10 @@ int Batch::advanceChunk(int nSteps, double *telDev, int telEvery, long long telB
         a.D = dD; a.S = dS; a.ctl = dCtl; a.nInst = nInst; a.nSteps = nSteps; a.stepBase = stepCount;
         a.nKeys = nKeys; a.keyStep = dKeyStep; a.keyThrottle = dKeyThr; a.keyDynoSpeed = dKeyDyno;
         a.stream = dStream; a.channels = channels; a.telemetry = telDev; a.telemetryEvery = telEvery; a.telemetryBase = telBase;
+        if (sessionStepsPerTick > 0 && dTickInputs) {
+            a.stepsPerTick = sessionStepsPerTick; a.nTicks = sessionTicks; a.tickStride = sessionStride; a.sessionBase = sessionBase;
+            a.tickInputs = dTickInputs; a.sessionDynoMaxTorque = sessionDynoMaxTorque; a.tickLog = dTickLog;
+        }
         markBegin(0);
         ESB_CUDA(esbLaunchPhysics(a, hostD, blockThreads, instPerWarp, kernelVariant, stream));
         markEnd();

@@ -129,6 +129,12 @@ int32_t EsbBatchSetSolver(EsbBatchHandle h, int32_t maxIt, double minDelta, doub
 }
 int32_t EsbBatchSetSineMode(EsbBatchHandle h, int32_t en) { if (!h) return ESIM_ERROR_INVALID_HANDLE; h->b.sineMode = en != 0; return ESIM_SUCCESS; }
 int32_t EsbBatchSetControls(EsbBatchHandle h, int32_t first, int32_t count, const EsbControls *c) { return h ? h->b.setControls(first, count, c) : ESIM_ERROR_INVALID_HANDLE; }
+int32_t EsbBatchSetSession(EsbBatchHandle h, int32_t nTicks, int32_t stepsPerTick, const double *inputs, int32_t stride, double dynoMaxTorque) {
+    return h ? h->b.setSession(nTicks, stepsPerTick, inputs, stride, dynoMaxTorque) : ESIM_ERROR_INVALID_HANDLE;
+}
+int32_t EsbBatchGetSessionLog(EsbBatchHandle h, double *out, int32_t maxTicks, int32_t *outTicks) {
+    return h ? h->b.getSessionLog(out, maxTicks, outTicks) : ESIM_ERROR_INVALID_HANDLE;
+}
 int32_t EsbBatchSetGear(EsbBatchHandle h, int32_t first, int32_t count, const int32_t *gears) { return h ? h->b.setGear(first, count, gears) : ESIM_ERROR_INVALID_HANDLE; }
 int32_t EsbBatchGetControls(EsbBatchHandle h, int32_t inst, EsbControls *out) {
     if (!h) return ESIM_ERROR_INVALID_HANDLE;

@@ -32,7 +32,10 @@ enum EsbGlobalField {
     ESB_GF_LAST_ITER,
     ESB_GF_TOTAL_EXH_FLOW,
     ESB_GF_VEH_INV_INERTIA,                    /* 1 / I of the vehicle-mass body: 1 until a forward gear is selected (changeGear) */
-    ESB_GF_EXACT_OPS,                          /* diagnostic: gas operations of this instance that left the straight-line arithmetic
+    ESB_GF_SESSION,                            /* start / stop state machine of the instance (device-side session, physics_run.cuh): phase,
+                                                  starter engaged, ticks, exhaust-flow sum, exhaust-flow baseline, rpm and exhaust flow
+                                                  at the end of the last tick */
+    ESB_GF_EXACT_OPS = ESB_GF_SESSION + 7,                          /* diagnostic: gas operations of this instance that left the straight-line arithmetic
                                                   (an operand outside its exact range) and were redone with plain IEEE / and sqrt */
     ESB_GF_PLENUM,                             /* ESB_MAX_INTAKE x cell(8) */
     ESB_GF_COLLECTOR = ESB_GF_PLENUM + 8 * ESB_MAX_INTAKE, /* ESB_MAX_EXHAUST x cell(8) */

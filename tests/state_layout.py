@@ -17,8 +17,9 @@ GF_CLUTCH_TORQUE = 25
 GF_LAST_ITER = 26
 GF_TOTAL_EXH_FLOW = 27
 GF_VEH_INV_INERTIA = 28
-GF_EXACT_OPS = 29
-GF_PLENUM = 30
+GF_SESSION = 29
+GF_EXACT_OPS = 36
+GF_PLENUM = 37
 GF_COLLECTOR = GF_PLENUM + 8 * MAX_INTAKE
 GF_COUNT = GF_COLLECTOR + 8 * MAX_EXHAUST
 CF_PISTON, CF_ROD, CF_LAMBDA, CF_CHAMBER, CF_INTAKE_RUNNER, CF_EXHAUST_RUNNER = 0, 6, 12, 17, 25, 33
