@@ -57,6 +57,10 @@ def main():
     stream = torch.cuda.current_stream().cuda_stream
     rows_per_ir = C // args.irs
 
+    other_ir = 5 % args.irs                      # with several IRs: a few rows of another response are checked as well
+    other_row = other_ir * rows_per_ir
+    keep2 = torch.zeros((8, min(args.check_samples, N)), dtype=torch.float32, device=dev)
+
     def run_all(keep=None):
         n0 = 0
         while n0 < N:
@@ -66,6 +70,7 @@ def main():
             if keep is not None and n0 < keep.shape[1]:
                 m = min(cnt, keep.shape[1] - n0)
                 keep[:, n0:n0 + m] = Y[:keep.shape[0], :m]
+                keep2[:, n0:n0 + m] = Y[other_row:other_row + 8, :m]
             n0 += cnt
 
     # correctness on a subset (first launch doubles as warm-up)
@@ -82,6 +87,9 @@ def main():
     def snr(ref, test):
         return 10 * math.log10((ref ** 2).sum() / max(((test - ref) ** 2).sum(), 1e-300))
     snr_fft = min(snr(ref_fft[r], got[r]) for r in range(64))
+    x2 = X[other_row:other_row + 8, hist:hist + nchk].cpu().numpy().astype(np.float64)
+    ref2 = fftconvolve(x2, h[other_ir].cpu().numpy().astype(np.float64)[None, :], mode="full", axes=1)[:, :nchk]
+    snr_other = min(snr(ref2[r], keep2.cpu().numpy().astype(np.float64)[r]) for r in range(8))
     snr_direct = None
     if args.check_channels > 0:
         sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -111,7 +119,7 @@ def main():
         "roofline": {"bound": "fp32", "achieved": flop / (best * 1e-3) * 1e-12, "peak": peak, "unit": "TFLOP/s",
                      "frac": flop / (best * 1e-3) * 1e-12 / peak, "peak_source": "measured live: register-resident FFMA loop (EsbProbePeak)"},
         "audio_seconds_per_wall_second": C * (N / 44100.0) / (best * 1e-3),
-        "snr_db_vs_fp64_fft_64ch": snr_fft, "snr_db_vs_oracle_direct_fp64": snr_direct,
+        "snr_db_vs_fp64_fft_64ch": snr_fft, "snr_db_vs_fp64_fft_rows_of_ir_%d" % other_ir: snr_other, "snr_db_vs_oracle_direct_fp64": snr_direct,
     }
     print(json.dumps(line), flush=True)
 

@@ -209,7 +209,11 @@ int Batch::reset() {
         return ESIM_ERROR_INVALID_PARAMETER;
     }
     ESB_CUDA(cudaSetDevice(device));
-    deriveDeviceParams(params, simFreq, cfg.fluidSimulationSteps, solverMaxIt, solverMinDelta, solverBeta, cfg.seed, hostD);
+    // Lanes per instance (results do not depend on it).  Measured on B200 (profiles/bench_r02_lanes.json): 8 lanes for every engine up to
+    // 8 cylinders - four exchange pairs per slot shorten the step of a small engine (EJ25 +20 %, a single +72 %) - and 16 lanes while the
+    // batch is small enough to leave the machine under-filled anyway (<= 2048 instances: V8 +16 % at 256 and 1024, +3 % at 2048).
+    const int minLanes = (nInst <= 2048) ? 16 : 8;
+    deriveDeviceParams(params, simFreq, cfg.fluidSimulationSteps, solverMaxIt, solverMinDelta, solverBeta, cfg.seed, hostD, minLanes);
     lanes = hostD.lanesPerInstance;
     if (!dD) ESB_CUDA(cudaMalloc(&dD, sizeof(EsbDeviceParams)));
     ESB_CUDA(cudaMemcpyAsync(dD, &hostD, sizeof(EsbDeviceParams), cudaMemcpyHostToDevice, stream));

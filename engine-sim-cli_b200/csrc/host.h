@@ -36,9 +36,9 @@ bool readWav(const std::string &path, WavData &out, std::string &err);
 bool writeWavMono16(const std::string &path, const int16_t *samples, size_t n, int sampleRate, std::string &err);
 
 // instance_init.cpp — derived constants and the initial state column of an instance
-int lanesForCylinders(int n);
+int lanesForCylinders(int n, int minLanes = 1);
 void deriveDeviceParams(const EsbEngineParams &P, double simFreq, int fluidSteps, int maxIterations, double minDelta, double beta,
-                        uint64_t seedBase, EsbDeviceParams &D);
+                        uint64_t seedBase, EsbDeviceParams &D, int minLanes = 1);
 void initialStateColumn(const EsbDeviceParams &D, std::vector<double> &col);
 // gas_schedule.cpp — gas-network tables and the slot schedule of one step (called by deriveDeviceParams)
 void buildGasNet(const EsbEngineParams &P, EsbDeviceParams &D);

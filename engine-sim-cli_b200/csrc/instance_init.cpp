@@ -11,6 +11,7 @@
 #include "esb_math.h"
 
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <stdexcept>
 
@@ -38,14 +39,17 @@ void putCell(std::vector<double> &col, int field, int stride, const CellInit &c)
 }
 } // namespace
 
-int lanesForCylinders(int n) {
+// Lanes per instance: a power of two >= the cylinder count (lane c owns cylinder c's rigid bodies), and at least minLanes: the gas
+// network is scheduled over lane PAIRS whatever the cylinder count (gas_schedule.cpp), so a small engine on more lanes has more
+// exchanges in flight per slot and a shorter step, at the price of fewer instances per warp.
+int lanesForCylinders(int n, int minLanes) {
     int g = 1;
-    while (g < n) g <<= 1;
+    while (g < n || g < minLanes) g <<= 1;
     return g;
 }
 
 void deriveDeviceParams(const EsbEngineParams &P, double simFreq, int fluidSteps, int maxIterations, double minDelta, double beta,
-                        uint64_t seedBase, EsbDeviceParams &D) {
+                        uint64_t seedBase, EsbDeviceParams &D, int minLanes) {
     std::memset(&D, 0, sizeof(D));
     D.P = P;
     if (P.cylinderCount < 1 || P.cylinderCount > ESB_MAX_CYL) throw std::runtime_error("cylinderCount out of range");
@@ -56,7 +60,8 @@ void deriveDeviceParams(const EsbEngineParams &P, double simFreq, int fluidSteps
     D.speedFilterAlpha = D.dt / (0.01 + D.dt);
     D.attenuationSpeed = 40.0 * kPi / 30.0;
     D.solverBeta = beta; D.solverMinDelta = minDelta; D.solverMaxIterations = maxIterations;
-    D.lanesPerInstance = lanesForCylinders(P.cylinderCount);
+    if (const char *e = std::getenv("ESB_MIN_LANES")) minLanes = std::atoi(e);   // developer override (tools/bench_engines_quick.sh)
+    D.lanesPerInstance = lanesForCylinders(P.cylinderCount, minLanes < 1 ? 1 : (minLanes > 16 ? 16 : minLanes));
     D.seedBase = seedBase;
     D.invCrankMass = 1.0 / (P.crankMass + P.flywheelMass);
     D.invCrankInertia = 1.0 / P.crankMomentOfInertia;
