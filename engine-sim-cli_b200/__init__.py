@@ -7,4 +7,4 @@ extension the offline renderer uses.  All arithmetic runs in the CUDA kernels of
 libenginesim_b200.so; there is no CPU path, and importing the API without the built library
 raises."""
 from .api import (BatchSimulator, MultiBatchSimulator, Controls, EngineSimError, Simulator, lib, library_path, ESIM_SUCCESS,  # noqa: F401
-                  fir_run, probe_peak, check_fast_arith, state_fields, params_size, compile_script, script_library_root, TELEMETRY_STRIDE)
+                  fir_run, probe_peak, check_fast_arith, check_fast_arith_noalloc, NOALLOC_MAX_N, state_fields, params_size, compile_script, script_library_root, TELEMETRY_STRIDE)

@@ -112,7 +112,7 @@ def lib():
             "EsbMultiLoadEngineFile": [vp, i32, C.c_char_p, C.c_char_p], "EsbMultiLoadParams": [vp, i32, vp],
             "EsbMultiSetImpulseResponse": [vp, i32, i32, vp, i32, flt, i32], "EsbMultiSamplesFor": [vp, i32, C.POINTER(i32)],
             "EsbMultiRender": [vp, i32, vp, i64, vp], "EsbMultiWriteWavs": [vp, C.c_char_p, C.c_char_p], "EsbMultiGetStats": [vp, i32, vp],
-            "EsbCheckFastArith": [i32, i32, vp, vp, vp, vp],
+            "EsbCheckFastArith": [i32, i32, vp, vp, vp, vp], "EsbCheckFastArithNoAlloc": [i32, i32, vp, vp, vp, vp],
             "EngineSimCreate": [vp, C.POINTER(vp)], "EngineSimLoadScript": [vp, C.c_char_p, C.c_char_p], "EngineSimLoadParams": [vp, vp, vp, i32, flt],
             "EngineSimDestroy": [vp], "EngineSimSetThrottle": [vp, dbl], "EngineSimSetSpeedControl": [vp, dbl], "EngineSimSetIgnition": [vp, i32],
             "EngineSimSetStarterMotor": [vp, i32], "EngineSimSetDyno": [vp, i32, i32, dbl, dbl], "EngineSimSetClutchPressure": [vp, dbl],
@@ -574,4 +574,19 @@ def check_fast_arith(op, a, b=None):
     rc = lib().EsbCheckFastArith(op, a.size, _ptr(a), _ptr(b), _ptr(out), _ptr(flagged))
     if rc != 0:
         raise EngineSimError(rc, "EsbCheckFastArith failed")
+    return out, flagged
+
+
+NOALLOC_MAX_N = 65536  # ESB_NOALLOC_MAX_N
+
+
+def check_fast_arith_noalloc(op, a, b=None):
+    """check_fast_arith through EsbCheckFastArithNoAlloc: device staging in the library's fixed array, no device allocation."""
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    b = np.ascontiguousarray(b, dtype=np.float64) if b is not None else None
+    out = np.zeros_like(a)
+    flagged = np.zeros(a.shape, dtype=np.uint32)
+    rc = lib().EsbCheckFastArithNoAlloc(op, a.size, _ptr(a), _ptr(b), _ptr(out), _ptr(flagged))
+    if rc != 0:
+        raise EngineSimError(rc, (lib().EsbBatchGetLastError(None) or b"").decode() or "EsbCheckFastArithNoAlloc failed")
     return out, flagged

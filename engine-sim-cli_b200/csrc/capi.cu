@@ -8,7 +8,9 @@
 #include <cstring>
 #include <deque>
 #include <memory>
+#include <mutex>
 #include <new>
+#include <string>
 #include <thread>
 
 using esb::Batch;
@@ -244,6 +246,64 @@ int32_t EsbCheckFastArith(int32_t op, int32_t n, const double *a, const double *
     ok = ok && cudaMemcpy(flagged, dF, (size_t)n * sizeof(unsigned), cudaMemcpyDeviceToHost) == cudaSuccess;
     cudaFree(dA); cudaFree(dB); cudaFree(dO); cudaFree(dF);
     return ok ? ESIM_SUCCESS : ESIM_ERROR_CUDA;
+}
+
+// ---------------------------------------------------------------------------------------
+// EsbCheckFastArithNoAlloc: the same check with its device staging (a, b, out, flagged) in a file-scope device array instead of
+// four cudaMalloc'd buffers, for callers that may not allocate (graph capture, serving loops).  No counterpart in the reference.
+// In host code `g_noAllocScratch` is only the symbol's stand-in; the device address comes from cudaGetSymbolAddress, once per device.
+#define ESB_NOALLOC_BYTES ((size_t)ESB_NOALLOC_MAX_N * (3 * sizeof(double) + sizeof(unsigned)))
+static __device__ __align__(256) unsigned char g_noAllocScratch[ESB_NOALLOC_BYTES];
+
+namespace {
+constexpr int kNoAllocMaxDevices = 64;
+std::mutex g_noAllocMutex;
+unsigned char *g_noAllocBase[kNoAllocMaxDevices] = {};
+
+// device address of the scratch array on the CURRENT device (looked up on first use there)
+int noAllocScratch(unsigned char **out) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kNoAllocMaxDevices) { g_createError = "EsbCheckFastArithNoAlloc: no current CUDA device"; return ESIM_ERROR_NOT_INITIALIZED; }
+    std::lock_guard<std::mutex> lock(g_noAllocMutex);
+    if (!g_noAllocBase[dev]) {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noAllocScratch);
+        if (e != cudaSuccess || !p) {
+            g_createError = std::string("EsbCheckFastArithNoAlloc: cudaGetSymbolAddress failed on device ") + std::to_string(dev) + ": " + cudaGetErrorString(e);
+            return ESIM_ERROR_CUDA;
+        }
+        g_noAllocBase[dev] = static_cast<unsigned char *>(p);
+    }
+    *out = g_noAllocBase[dev];
+    return ESIM_SUCCESS;
+}
+} // namespace
+
+int32_t EsbCheckFastArithNoAlloc(int32_t op, int32_t n, const double *a, const double *b, double *out, uint32_t *flagged) {
+    if (n <= 0 || !a || !out || !flagged || (op == 0 && !b) || (op != 0 && op != 1)) { g_createError = "EsbCheckFastArithNoAlloc: invalid argument"; return ESIM_ERROR_INVALID_PARAMETER; }
+    if (n > ESB_NOALLOC_MAX_N) {
+        g_createError = "EsbCheckFastArithNoAlloc: n = " + std::to_string(n) + " exceeds the fixed scratch of ESB_NOALLOC_MAX_N = " + std::to_string(ESB_NOALLOC_MAX_N) +
+                        " values; split the call or use EsbCheckFastArith";
+        return ESIM_ERROR_INVALID_PARAMETER;
+    }
+    unsigned char *base = nullptr;
+    const int rc = noAllocScratch(&base);
+    if (rc != ESIM_SUCCESS) return rc;
+    // fixed partition of the array, so that a short call never aliases another call's regions
+    double *dA = reinterpret_cast<double *>(base);
+    double *dB = dA + ESB_NOALLOC_MAX_N;
+    double *dO = dB + ESB_NOALLOC_MAX_N;
+    unsigned *dF = reinterpret_cast<unsigned *>(dO + ESB_NOALLOC_MAX_N);
+    const size_t bytes = (size_t)n * sizeof(double), fbytes = (size_t)n * sizeof(unsigned);
+    // the array keeps the previous call's contents: the result regions start from zero
+    bool ok = cudaMemsetAsync(dO, 0, bytes, 0) == cudaSuccess && cudaMemsetAsync(dF, 0, fbytes, 0) == cudaSuccess;
+    ok = ok && cudaMemcpy(dA, a, bytes, cudaMemcpyHostToDevice) == cudaSuccess;
+    ok = ok && cudaMemcpy(dB, b ? b : a, bytes, cudaMemcpyHostToDevice) == cudaSuccess;
+    ok = ok && esbLaunchFastArCheck(op, n, dA, dB, dO, dF, 0) == cudaSuccess;
+    ok = ok && cudaMemcpy(out, dO, bytes, cudaMemcpyDeviceToHost) == cudaSuccess;
+    ok = ok && cudaMemcpy(flagged, dF, fbytes, cudaMemcpyDeviceToHost) == cudaSuccess;
+    if (!ok) { g_createError = std::string("EsbCheckFastArithNoAlloc: ") + cudaGetErrorString(cudaGetLastError()); return ESIM_ERROR_CUDA; }
+    return ESIM_SUCCESS;
 }
 
 int32_t EsbGetLayout(int32_t *outParamsBytes, int32_t *outStateFields) {

@@ -253,6 +253,15 @@ int32_t EsbGetLayout(int32_t *outParamsBytes, int32_t *outStateFields);
 /* Self-check of the physics kernel's branch-free division (op 0: out = a / b) and square root (op 1: out = sqrt(a)):
  * HOST arrays of n doubles; flagged[i] = 1 where the kernel would fall back to the plain IEEE operation instead. */
 int32_t EsbCheckFastArith(int32_t op, int32_t n, const double *a, const double *b, double *out, uint32_t *flagged);
+/* The same check for callers that must not allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.  Same arguments, results and
+ * error codes as EsbCheckFastArith, but the device staging of a, b, out and flagged lives in one fixed array inside the library
+ * (ESB_NOALLOC_MAX_N values of each, 1.75 MiB, held by every GPU that loads the library until the process exits); the call performs no
+ * cudaMalloc / cudaFree.  n > ESB_NOALLOC_MAX_N fails with ESIM_ERROR_INVALID_PARAMETER and a message in EsbBatchGetLastError(NULL).
+ * Runs on the current device's default stream and returns when the results are in the host arrays.  Every call on a device shares
+ * the array: calls that overlap on one GPU (several host threads, or several processes' worth of streams) race - serialise them. */
+#define ESB_NOALLOC_MAX_N 65536
+int32_t EsbCheckFastArithNoAlloc(int32_t op, int32_t n, const double *a, const double *b, double *out, uint32_t *flagged);
 
 #ifdef __cplusplus
 }
