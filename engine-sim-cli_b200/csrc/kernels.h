@@ -62,7 +62,7 @@ struct EsbFirArgs {
     long long yStride;
 };
 #define ESB_MAX_SAMPLES_PER_STEP 64 /* K3 stage size: ceil(sampleRate / simFreq) + 1 must not exceed it */
-#define ESB_FIR_KT 256
+#define ESB_FIR_KT 128
 #define ESB_FIR_T 192
 cudaError_t esbLaunchFir(const EsbFirArgs &a, cudaStream_t stream);
 int esbFirSmemBytes();
