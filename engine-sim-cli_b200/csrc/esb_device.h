@@ -124,11 +124,13 @@ typedef struct EsbGasExchange {   /* GasSystem::flow(FlowParameters) between cel
     int32_t cell0, cell1;
     int32_t kSource;              /* index into the per-step k array: valve k of a cylinder (c intake, N + c exhaust), inlet k of intake i (2N + i) */
     int32_t flowCylinder;         /* >= 0: the exhaust-valve exchange of that cylinder; its flow goes into the step's exhaust-flow total */
+    int32_t off0, off1;           /* where the kernel finds the two cells: >= 0: bytes from the instance's first cell; < 0: ~off bytes from the
+                                     first constant cell (never stored) */
 } EsbGasExchange;
 
 typedef struct EsbGasRelax {      /* dissipateExcessVelocity + updateVelocity of one cell */
     double beta, width, height, dx, dy;
-    int32_t cell, pad;
+    int32_t cell, off;            /* off: bytes from the instance's first cell */
 } EsbGasRelax;
 
 typedef struct EsbGasNet {
@@ -139,7 +141,8 @@ typedef struct EsbGasNet {
     EsbGasRelax relax[ESB_GAS_MAX_RELAX];
     double constCells[ESB_GAS_MAX_CONST][8];
     uint8_t slotType[ESB_GAS_MAX_SLOTS];
-    uint16_t slotOps[ESB_GAS_MAX_SLOTS * 16];    /* [slot][entry]: operation index | substep << 8 ; ESB_GAS_IDLE in the low byte = idle */
+    uint32_t slotOps[ESB_GAS_MAX_SLOTS * 16];    /* [slot][entry]: operation index (ESB_GAS_IDLE = idle) in the low byte; bits 16..31: 1 + index into the
+                                                    step's exhaust-valve flow record [substep][cylinder] where the lane records its exchange's flow, else 0 */
 } EsbGasNet;
 
 typedef struct EsbDeviceParams {

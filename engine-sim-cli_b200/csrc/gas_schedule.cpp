@@ -69,14 +69,17 @@ void buildGasNet(const EsbEngineParams &P, EsbDeviceParams &D) {
     }
 
     // operation tables
+    const int cellBytes = ESB_GAS_CELL_STRIDE * (int)sizeof(double);
+    auto cellOffset = [&](int cell) { return cell < g.nCells ? cell * cellBytes : ~((cell - g.nCells) * cellBytes); };
     auto addExchange = [&](int c0, int c1, double k, int kSource, double dx, double dy, double a0, double a1, int flowCyl) {
         EsbGasExchange &e = g.exchange[g.nExchange];
         e.cell0 = c0; e.cell1 = c1; e.kConst = k; e.kSource = kSource; e.dirx = dx; e.diry = dy; e.area0 = a0; e.area1 = a1; e.flowCylinder = flowCyl;
+        e.off0 = cellOffset(c0); e.off1 = cellOffset(c1);
         return g.nExchange++;
     };
     auto addRelax = [&](int cell, double beta, double w, double h, double dx, double dy) {
         EsbGasRelax &r = g.relax[g.nRelax];
-        r.cell = cell; r.beta = beta; r.width = w; r.height = h; r.dx = dx; r.dy = dy;
+        r.cell = cell; r.off = cell * cellBytes; r.beta = beta; r.width = w; r.height = h; r.dx = dx; r.dy = dy;
         return g.nRelax++;
     };
     std::vector<int> exInlet(nIn), exIdle(nIn, -1), rxPlenum(nIn), exOutlet(nEx), rxCollector(nEx);
@@ -108,6 +111,7 @@ void buildGasNet(const EsbEngineParams &P, EsbDeviceParams &D) {
     {   // the idle exchange: two cells at rest, nothing flows, nothing is stored
         EsbGasExchange &e = g.exchange[g.nExchange];
         e.cell0 = rest; e.cell1 = rest; e.kConst = 0; e.kSource = -1; e.dirx = 1.0; e.diry = 0.0; e.area0 = 10.0; e.area1 = 10.0; e.flowCylinder = -1;
+        e.off0 = cellOffset(rest); e.off1 = cellOffset(rest);
     }
 
     // the step's operations in the reference's order
@@ -242,26 +246,27 @@ void buildGasNet(const EsbEngineParams &P, EsbDeviceParams &D) {
     if (nSlots > ESB_GAS_MAX_SLOTS) throw std::runtime_error("gas schedule does not fit (too many fluid substeps for this engine)");
     for (int sl = 0; sl < nSlots; ++sl) {
         const int type = bestSlotKind[sl];
-        uint16_t *row = &g.slotOps[(size_t)sl * 16];
+        uint32_t *row = &g.slotOps[(size_t)sl * 16];
         for (int l = 0; l < 16; ++l) row[l] = ESB_GAS_IDLE;
         g.slotType[sl] = (uint8_t)type;
         int used = 0;
         for (int j = 0; j < nOps; ++j) {   // operations of a slot in the reference's order
             if (bestSlotOf[j] != sl) continue;
-            const uint16_t entry = (uint16_t)(ops[j].kind | (ops[j].sub << 8));
+            const uint32_t entry = (uint32_t)ops[j].kind;
             if (type == ESB_SLOT_EXCHANGE) {
-                row[used] = entry;
+                const int flowCyl = g.exchange[ops[j].kind].flowCylinder;
+                row[used] = entry | (flowCyl >= 0 ? (uint32_t)(ops[j].sub * N + flowCyl + 1) << 16 : 0u);   // the first lane of the pair records the flow
                 if (g.split) row[used + G / 2] = entry;   // the partner lane of the pair
             } else if (type == ESB_SLOT_RELAX) {
                 row[used] = entry;
             } else {
-                for (int l = 0; l < N; ++l) row[l] = (P.cyl[l].blowbyK != 0) ? entry : (uint16_t)ESB_GAS_IDLE;   // lane c: cylinder c
+                for (int l = 0; l < N; ++l) row[l] = (P.cyl[l].blowbyK != 0) ? entry : (uint32_t)ESB_GAS_IDLE;   // lane c: cylinder c
             }
             ++used;
         }
     }
     g.nSlots = nSlots;
-    if (D.fluidSteps > 255) throw std::runtime_error("fluidSimulationSteps out of range");
+    if (D.fluidSteps * N > 65534 || D.fluidSteps > 255) throw std::runtime_error("fluidSimulationSteps out of range");
 }
 
 } // namespace esb

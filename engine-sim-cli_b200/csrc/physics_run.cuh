@@ -94,7 +94,7 @@ inline GasSmemLayout gasSmemLayout(const EsbGasNet &gn, int nCyl, int nIntakes, 
     GasSmemLayout L;
     L.offType = 0;
     L.offOps = up((unsigned)gn.nSlots);
-    L.offExchange = L.offOps + up((unsigned)(gn.nSlots * gn.entriesPerSlot * sizeof(uint16_t)));
+    L.offExchange = L.offOps + up((unsigned)(gn.nSlots * gn.entriesPerSlot * sizeof(uint32_t)));
     L.offRelax = L.offExchange + up((unsigned)((gn.nExchange + 1) * sizeof(EsbGasExchange)));
     L.offGasConst = L.offRelax + up((unsigned)(gn.nRelax * sizeof(EsbGasRelax)));
     L.offConst = L.offGasConst + up((unsigned)sizeof(GasConst));
@@ -109,7 +109,7 @@ inline GasSmemLayout gasSmemLayout(const EsbGasNet &gn, int nCyl, int nIntakes, 
 ESB_DEV GasView gasViewAt(unsigned char *base, const GasSmemLayout &L, const EsbGasNet &gn, int group) {
     GasView v;
     v.slotType = base + L.offType;
-    v.slotOps = reinterpret_cast<const uint16_t *>(base + L.offOps);
+    v.slotOps = reinterpret_cast<const uint32_t *>(base + L.offOps);
     v.exchange = reinterpret_cast<const EsbGasExchange *>(base + L.offExchange);
     v.relax = reinterpret_cast<const EsbGasRelax *>(base + L.offRelax);
     v.constCells = reinterpret_cast<const double *>(base + L.offConst);
@@ -119,6 +119,7 @@ ESB_DEV GasView gasViewAt(unsigned char *base, const GasSmemLayout &L, const Esb
     v.flows = v.kStep + L.kStepDoubles;
     v.exactOps = v.flows + L.flowDoubles;
     v.nSlots = gn.nSlots; v.entries = gn.entriesPerSlot; v.nCells = gn.nCells; v.nExchange = gn.nExchange;
+    v.cellsRef = cellRefOf(v.cells); v.constRef = cellRefOf(v.constCells);
     return v;
 }
 // Copies the tables into the block's shared memory: element i of each table by thread (tid + k * nThreads).
@@ -126,7 +127,7 @@ ESB_DEV void gasTablesToShared(unsigned char *base, const GasSmemLayout &L, cons
     const EsbGasNet &gn = D->gas;
     if (tid == 0) *reinterpret_cast<GasConst *>(base + L.offGasConst) = makeGasConst(D->hcr, D->chokedFlowLimit, D->chokedFlowFactor);
     for (int i = tid; i < gn.nSlots; i += nThreads) base[L.offType + i] = gn.slotType[i];
-    uint16_t *ops = reinterpret_cast<uint16_t *>(base + L.offOps);
+    uint32_t *ops = reinterpret_cast<uint32_t *>(base + L.offOps);
     for (int i = tid; i < gn.nSlots * gn.entriesPerSlot; i += nThreads) ops[i] = gn.slotOps[(i / gn.entriesPerSlot) * 16 + (i % gn.entriesPerSlot)];
     int *ex = reinterpret_cast<int *>(base + L.offExchange);
     const int *exSrc = reinterpret_cast<const int *>(gn.exchange);

@@ -15,8 +15,8 @@ import bench
 import engine_sim_cli_b200 as esb
 from engine_sim_cli_b200 import api
 
-NAMES = ["prelude", "solver", "ignition+chamber+valveK", "gas schedule (unattributed)", "slot barrier", "exchange slot", "relax slot", "",
-         "", "totals+audio", "slot table read", "", "", "", "", ""]
+NAMES = ["prelude", "solver: integrate", "intake flow constants", "gas schedule (unattributed)", "slot barrier", "exchange slot", "relax slot", "speed filter + ignition",
+         "chamber update", "totals+audio", "slot table read", "valve flow constants", "solver: set-up", "solver: sweeps", "", ""]
 
 
 def run(n, steps=300, settle=1500):
