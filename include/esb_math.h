@@ -88,6 +88,23 @@ ESB_HD void esb_sincos(double x, double *s_out, double *c_out) {
 ESB_HD double esb_sin(double x) { double s, c; esb_sincos(x, &s, &c); return s; }
 ESB_HD double esb_cos(double x) { double s, c; esb_sincos(x, &s, &c); return c; }
 
+/* Polynomial coefficients of log / exp: literals on the host; on the device a __constant__ table, so that the FP64 instructions take
+ * them as constant-bank operands instead of holding every coefficient in a register pair for the whole of a caller (same values). */
+#if defined(__CUDA_ARCH__) && defined(ESB_MATH_CONSTANT_TABLE)
+#define ESB_K(i, literal) esbMathK[i]
+#else
+#define ESB_K(i, literal) (literal)
+#endif
+#if defined(__CUDACC__) && defined(ESB_MATH_CONSTANT_TABLE)
+static __constant__ double esbMathK[16] = {
+    6.93147180369123816490e-01, 1.90821492927058770002e-10,
+    1.531383769920937332e-01, 2.222219843214978396e-01, 3.999999999940941908e-01,
+    1.479819860511658591e-01, 1.818357216161805012e-01, 2.857142874366239149e-01, 6.666666666666735130e-01,
+    1.44269504088896338700e+00,
+    4.13813679705723846039e-08, -1.65339022054652515390e-06, 6.61375632143793436117e-05, -2.77777777770155933842e-03, 1.66666666666666019037e-01,
+    0.0};
+#endif
+
 /* ---- log / exp / pow ------------------------------------------------------ */
 /* Each contains one division.  The bodies are written once, over a divider `dv`, so the CUDA
  * physics kernel can supply its straight-line correctly-rounded division (physics_core.cuh
@@ -107,8 +124,8 @@ struct EsbIeeeDiv {
 
 /* x > 0, finite, normal. */
 ESB_DIV_TEMPLATE ESB_HD double esb_log_t(double x ESB_DIV_ARG) {
-    const double LN2_HI = 6.93147180369123816490e-01;
-    const double LN2_LO = 1.90821492927058770002e-10;
+    const double LN2_HI = ESB_K(0, 6.93147180369123816490e-01);
+    const double LN2_LO = ESB_K(1, 1.90821492927058770002e-10);
     int64_t b = esb_d2bits(x);
     int64_t e = ((b >> 52) & 0x7ff) - 1023;
     int64_t mant = b & 0x000fffffffffffffLL;
@@ -120,8 +137,8 @@ ESB_DIV_TEMPLATE ESB_HD double esb_log_t(double x ESB_DIV_ARG) {
     double s = ESB_DIV(f, 2.0 + f);
     double z = s * s;
     double w = z * z;
-    double t1 = w * esb_fma(w, esb_fma(w, 1.531383769920937332e-01, 2.222219843214978396e-01), 3.999999999940941908e-01);
-    double t2 = z * esb_fma(w, esb_fma(w, esb_fma(w, 1.479819860511658591e-01, 1.818357216161805012e-01), 2.857142874366239149e-01), 6.666666666666735130e-01);
+    double t1 = w * esb_fma(w, esb_fma(w, ESB_K(2, 1.531383769920937332e-01), ESB_K(3, 2.222219843214978396e-01)), ESB_K(4, 3.999999999940941908e-01));
+    double t2 = z * esb_fma(w, esb_fma(w, esb_fma(w, ESB_K(5, 1.479819860511658591e-01), ESB_K(6, 1.818357216161805012e-01)), ESB_K(7, 2.857142874366239149e-01)), ESB_K(8, 6.666666666666735130e-01));
     double R = t2 + t1;
     double hfsq = 0.5 * f * f;
     double dk = (double)e;
@@ -133,15 +150,15 @@ ESB_DIV_TEMPLATE ESB_HD double esb_exp_t(double x ESB_DIV_ARG) {
     const bool under = x < -700.0;
     if (x > 700.0) x = 700.0;
     if (under) x = -700.0;
-    const double LN2_HI = 6.93147180369123816490e-01;
-    const double LN2_LO = 1.90821492927058770002e-10;
-    const double INV_LN2 = 1.44269504088896338700e+00;
+    const double LN2_HI = ESB_K(0, 6.93147180369123816490e-01);
+    const double LN2_LO = ESB_K(1, 1.90821492927058770002e-10);
+    const double INV_LN2 = ESB_K(9, 1.44269504088896338700e+00);
     double kf = floor(x * INV_LN2 + 0.5);
     double hi = esb_fma(-kf, LN2_HI, x);
     double lo = kf * LN2_LO;
     double r = hi - lo;
     double t = r * r;
-    double c = r - t * esb_fma(t, esb_fma(t, esb_fma(t, esb_fma(t, 4.13813679705723846039e-08, -1.65339022054652515390e-06), 6.61375632143793436117e-05), -2.77777777770155933842e-03), 1.66666666666666019037e-01);
+    double c = r - t * esb_fma(t, esb_fma(t, esb_fma(t, esb_fma(t, ESB_K(10, 4.13813679705723846039e-08), ESB_K(11, -1.65339022054652515390e-06)), ESB_K(12, 6.61375632143793436117e-05)), ESB_K(13, -2.77777777770155933842e-03)), ESB_K(14, 1.66666666666666019037e-01));
     double y = 1.0 - ((lo - ESB_DIV(r * c, 2.0 - c)) - hi);
     int64_t k = (int64_t)kf;
     /* scale by 2^k (k within the normal range for our arguments) */
