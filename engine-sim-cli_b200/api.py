@@ -107,7 +107,7 @@ def lib():
             "EsbBatchGetLastStream": [vp, vp, i32, C.POINTER(i32)], "EsbBatchGetStats": [vp, i32, vp], "EsbBatchWriteWavs": [vp, C.c_char_p, C.c_char_p],
             "EsbBatchSetLaunchConfig": [vp, i32, i32], "EsbBatchGetLaunchCounts": [vp, vp],
             "EsbBatchSetProfiling": [vp, i32], "EsbBatchSetPhysicsShape": [vp, i32, i32], "EsbBatchGetKernelTimes": [vp, vp, vp],
-            "EsbFirRun": [vp, i64, i64, vp, i32, i32, i32, i32, i64, vp, i64, vp], "EsbProbePeak": [i32, i32, C.POINTER(dbl)], "EsbGetLayout": [C.POINTER(i32), C.POINTER(i32)], "EsbCompileScript": [C.c_char_p, C.c_char_p, i64, C.POINTER(i64)],
+            "EsbFirRun": [vp, i64, i64, vp, i32, i32, i32, i32, i64, vp, i64, vp], "EsbProbePeak": [i32, i32, C.POINTER(dbl)], "EsbGetLayout": [C.POINTER(i32), C.POINTER(i32)], "EsbGasScheduleInfo": [vp, i32, i32, C.POINTER(i32), C.POINTER(i32), C.c_char_p, i32], "EsbCompileScript": [C.c_char_p, C.c_char_p, i64, C.POINTER(i64)],
             "EsbMultiCreate": [i32, vp, vp, vp, C.POINTER(vp)], "EsbMultiDestroy": [vp], "EsbMultiGetShardBatch": [vp, i32, C.POINTER(vp)],
             "EsbMultiLoadEngineFile": [vp, i32, C.c_char_p, C.c_char_p], "EsbMultiLoadParams": [vp, i32, vp],
             "EsbMultiSetImpulseResponse": [vp, i32, i32, vp, i32, flt, i32], "EsbMultiSamplesFor": [vp, i32, C.POINTER(i32)],
@@ -563,6 +563,17 @@ def probe_peak(fp64, fma):
     if rc != ESIM_SUCCESS:
         raise EngineSimError(rc, "EsbProbePeak failed")
     return out.value
+
+
+def gas_schedule_info(params_blob, min_lanes=1, fluid_steps=8):
+    """The slot schedule of the fluid part of one step for this engine (no GPU needed): dict with the lanes per instance, the number of
+    exchange / relax / blow-by slots and `problem` ('' when every cell meets its operations in the reference's order)."""
+    buf = C.create_string_buffer(bytes(params_blob), len(params_blob))
+    lanes = C.c_int32()
+    slots = (C.c_int32 * 3)()
+    msg = C.create_string_buffer(256)
+    rc = lib().EsbGasScheduleInfo(C.cast(buf, C.c_void_p), min_lanes, fluid_steps, C.byref(lanes), slots, msg, 256)
+    return {"rc": rc, "lanes": lanes.value, "exchange_slots": slots[0], "relax_slots": slots[1], "blowby_slots": slots[2], "problem": msg.value.decode()}
 
 
 def check_fast_arith(op, a, b=None):

@@ -306,6 +306,24 @@ int32_t EsbCheckFastArithNoAlloc(int32_t op, int32_t n, const double *a, const d
     return ESIM_SUCCESS;
 }
 
+int32_t EsbGasScheduleInfo(const EsbEngineParams *params, int32_t minLanes, int32_t fluidSteps, int32_t *outLanes, int32_t *outSlots, char *outProblem, int32_t problemCapacity) {
+    if (!params) return ESIM_ERROR_INVALID_PARAMETER;
+    try {
+        auto D = std::make_unique<EsbDeviceParams>();
+        esb::deriveDeviceParams(*params, params->simulationFrequency > 0 ? params->simulationFrequency : 10000.0, fluidSteps > 0 ? fluidSteps : 8, 24, 1e-7, 0.2, 0, *D, minLanes);
+        if (outLanes) *outLanes = D->lanesPerInstance;
+        if (outSlots) {
+            outSlots[0] = outSlots[1] = outSlots[2] = 0;
+            for (int s = 0; s < D->gas.nSlots; ++s) ++outSlots[D->gas.slotType[s]];
+        }
+        const std::string problem = esb::checkGasSchedule(*params, *D);
+        if (outProblem && problemCapacity > 0) { std::snprintf(outProblem, (size_t)problemCapacity, "%s", problem.c_str()); }
+        return problem.empty() ? ESIM_SUCCESS : ESIM_ERROR_INVALID_PARAMETER;
+    } catch (const std::exception &e) {
+        if (outProblem && problemCapacity > 0) std::snprintf(outProblem, (size_t)problemCapacity, "%s", e.what());
+        return ESIM_ERROR_INVALID_PARAMETER;
+    }
+}
 int32_t EsbGetLayout(int32_t *outParamsBytes, int32_t *outStateFields) {
     if (outParamsBytes) *outParamsBytes = (int32_t)sizeof(EsbEngineParams);
     if (outStateFields) *outStateFields = ESB_STATE_FIELDS;

@@ -269,4 +269,91 @@ void buildGasNet(const EsbEngineParams &P, EsbDeviceParams &D) {
     if (D.fluidSteps * N > 65534 || D.fluidSteps > 255) throw std::runtime_error("fluidSimulationSteps out of range");
 }
 
+// Checks a built schedule against the sequential form it stands for: every operation of the step appears exactly once, no two
+// operations of a slot touch the same (stored) cell, and each cell meets its operations in the reference's order.  Returns an empty
+// string when the schedule is valid, else what is wrong (used by EsbGasScheduleInfo and the tests).
+std::string checkGasSchedule(const EsbEngineParams &P, const EsbDeviceParams &D) {
+    const EsbGasNet &g = D.gas;
+    const int N = P.cylinderCount, nIn = P.intakeCount, nEx = P.exhaustSystemCount, G = D.lanesPerInstance;
+    // the reference's sequence, per cell: (type, kind, substep) in order
+    struct Ref { int type, kind, sub; };
+    std::vector<std::vector<Ref>> want(g.nCells), got(g.nCells);
+    auto touch = [&](std::vector<std::vector<Ref>> &seq, int type, int kind, int sub) {
+        if (type == ESB_SLOT_EXCHANGE) {
+            const EsbGasExchange &e = g.exchange[kind];
+            if (e.cell0 < g.nCells) seq[e.cell0].push_back({type, kind, sub});
+            if (e.cell1 < g.nCells && e.cell1 != e.cell0) seq[e.cell1].push_back({type, kind, sub});
+        } else if (type == ESB_SLOT_RELAX) {
+            seq[g.relax[kind].cell].push_back({type, kind, sub});
+        }
+    };
+    // exchange / relax indices as buildGasNet lays them out
+    int ex = 0, rx = 0;
+    std::vector<int> exInlet(nIn), exIdle(nIn, -1), rxPlenum(nIn), exC(N), exP(N), exVI(N), exVE(N), rxIntr(N), rxExhr(N), exOutlet(nEx), rxCollector(nEx);
+    for (int i = 0; i < nIn; ++i) { exInlet[i] = ex++; if (P.intakes[i].idleFlowK != 0) exIdle[i] = ex++; rxPlenum[i] = rx++; }
+    for (int c = 0; c < N; ++c) { exC[c] = ex++; exP[c] = ex++; exVI[c] = ex++; exVE[c] = ex++; rxIntr[c] = rx++; rxExhr[c] = rx++; }
+    for (int e = 0; e < nEx; ++e) { exOutlet[e] = ex++; rxCollector[e] = rx++; }
+    if (ex != g.nExchange || rx != g.nRelax) return "operation tables do not match the engine";
+    long long wantOps = 0;
+    for (int s = 0; s < D.fluidSteps; ++s) {
+        for (int i = 0; i < nIn; ++i) {
+            touch(want, ESB_SLOT_EXCHANGE, exInlet[i], s); ++wantOps;
+            if (exIdle[i] >= 0) { touch(want, ESB_SLOT_EXCHANGE, exIdle[i], s); ++wantOps; }
+            touch(want, ESB_SLOT_RELAX, rxPlenum[i], s); ++wantOps;
+        }
+        for (int c = 0; c < N; ++c) {
+            touch(want, ESB_SLOT_EXCHANGE, exC[c], s); touch(want, ESB_SLOT_EXCHANGE, exP[c], s);
+            touch(want, ESB_SLOT_EXCHANGE, exVI[c], s); touch(want, ESB_SLOT_EXCHANGE, exVE[c], s);
+            touch(want, ESB_SLOT_RELAX, rxIntr[c], s); touch(want, ESB_SLOT_RELAX, rxExhr[c], s);
+            wantOps += 6;
+        }
+        for (int e = 0; e < nEx; ++e) { touch(want, ESB_SLOT_EXCHANGE, exOutlet[e], s); touch(want, ESB_SLOT_RELAX, rxCollector[e], s); wantOps += 2; }
+    }
+    // the schedule: which substep an entry belongs to is fixed by how often its operation has appeared before
+    std::vector<int> seenEx(g.nExchange, 0), seenRx(g.nRelax, 0);
+    long long gotOps = 0;
+    int blowbySlots = 0;
+    for (int sl = 0; sl < g.nSlots; ++sl) {
+        const int type = g.slotType[sl];
+        const uint32_t *row = &g.slotOps[(size_t)sl * 16];
+        std::vector<int> cellsInSlot;
+        if (type == ESB_SLOT_BLOWBY) { ++blowbySlots; continue; }
+        const int lanes = (type == ESB_SLOT_EXCHANGE && g.split) ? G / 2 : G;
+        for (int l = 0; l < lanes; ++l) {
+            const int kind = (int)(row[l] & 0xffu);
+            if (kind == ESB_GAS_IDLE) continue;
+            if (type == ESB_SLOT_EXCHANGE) {
+                if (kind >= g.nExchange) return "slot " + std::to_string(sl) + ": exchange index out of range";
+                if (g.split && (row[l + G / 2] & 0xffu) != (uint32_t)kind) return "slot " + std::to_string(sl) + ": the partner lane has a different operation";
+                const int sub = seenEx[kind]++;
+                const int flowCyl = g.exchange[kind].flowCylinder;
+                const uint32_t wantFlow = flowCyl >= 0 ? (uint32_t)(sub * N + flowCyl + 1) : 0u;
+                if ((row[l] >> 16) != wantFlow) return "slot " + std::to_string(sl) + ": flow record index";
+                touch(got, type, kind, sub);
+                const EsbGasExchange &e = g.exchange[kind];
+                if (e.cell0 < g.nCells) cellsInSlot.push_back(e.cell0);
+                if (e.cell1 < g.nCells) cellsInSlot.push_back(e.cell1);
+            } else {
+                if (kind >= g.nRelax) return "slot " + std::to_string(sl) + ": relax index out of range";
+                touch(got, type, kind, seenRx[kind]++);
+                cellsInSlot.push_back(g.relax[kind].cell);
+            }
+            ++gotOps;
+        }
+        std::sort(cellsInSlot.begin(), cellsInSlot.end());
+        if (std::adjacent_find(cellsInSlot.begin(), cellsInSlot.end()) != cellsInSlot.end()) return "slot " + std::to_string(sl) + ": two operations share a cell";
+    }
+    if (gotOps != wantOps) return "the schedule holds " + std::to_string(gotOps) + " operations, the step has " + std::to_string(wantOps);
+    bool anyBlowby = false;
+    for (int c = 0; c < N; ++c) anyBlowby = anyBlowby || P.cyl[c].blowbyK != 0;
+    if (blowbySlots != (anyBlowby ? D.fluidSteps : 0)) return "blow-by slots";
+    for (int c = 0; c < g.nCells; ++c) {
+        if (want[c].size() != got[c].size()) return "cell " + std::to_string(c) + ": operation count";
+        for (size_t j = 0; j < want[c].size(); ++j)
+            if (want[c][j].type != got[c][j].type || want[c][j].kind != got[c][j].kind || want[c][j].sub != got[c][j].sub)
+                return "cell " + std::to_string(c) + ": operation " + std::to_string(j) + " out of the reference's order";
+    }
+    return std::string();
+}
+
 } // namespace esb

@@ -42,5 +42,6 @@ void deriveDeviceParams(const EsbEngineParams &P, double simFreq, int fluidSteps
 void initialStateColumn(const EsbDeviceParams &D, std::vector<double> &col);
 // gas_schedule.cpp — gas-network tables and the slot schedule of one step (called by deriveDeviceParams)
 void buildGasNet(const EsbEngineParams &P, EsbDeviceParams &D);
+std::string checkGasSchedule(const EsbEngineParams &P, const EsbDeviceParams &D);   // "" = valid
 
 } // namespace esb

@@ -250,6 +250,11 @@ int32_t EsbCompileScript(const char *scriptPath, char *outJson, int64_t capacity
 /* Sizes of the binary contracts of this build: sizeof(EsbEngineParams) (the parameter blob of EsbBatchLoadParams /
  * EngineSimLoadParams) and the number of fields of the state block EsbBatchGetState returns. */
 int32_t EsbGetLayout(int32_t *outParamsBytes, int32_t *outStateFields);
+/* The slot schedule the library builds for the fluid part of one step of this engine (csrc/gas_schedule.cpp; the reference runs the same
+ * operations strictly in sequence, PistonEngineSimulator::simulateStep_, quoted at archive/TA2_FINDINGS.md:194-199): lanes per instance,
+ * outSlots[3] = exchange / relax / blow-by slots, and a check that every cell meets its operations in the reference's order
+ * (ESIM_SUCCESS; otherwise the problem as text).  No GPU needed. */
+int32_t EsbGasScheduleInfo(const EsbEngineParams *params, int32_t minLanes, int32_t fluidSteps, int32_t *outLanes, int32_t *outSlots, char *outProblem, int32_t problemCapacity);
 /* Self-check of the physics kernel's branch-free division (op 0: out = a / b) and square root (op 1: out = sqrt(a)):
  * HOST arrays of n doubles; flagged[i] = 1 where the kernel would fall back to the plain IEEE operation instead. */
 int32_t EsbCheckFastArith(int32_t op, int32_t n, const double *a, const double *b, double *out, uint32_t *flagged);

@@ -119,3 +119,26 @@ def test_reference_arm_rank_nonzero_is_silent():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "0"],
                        capture_output=True, text=True, env=env, timeout=120)
     assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+@pytest.mark.parametrize("engine,lanes,max_slots", [
+    ("gm_ls", 8, (74, 23)), ("gm_ls", 16, (74, 14)), ("gm_ls", 1, None), ("merlin_v12", 8, (108, 19)), ("lfa_v10", 8, (90, 15)),
+    ("radial_9", 8, (84, 18)), ("subaru_ej25", 8, (46, 23)), ("subaru_ej25", 4, None), ("hayabusa_i4", 8, None), ("honda_trx520", 8, None),
+])
+def test_gas_schedule_keeps_every_cells_operation_order(engine, lanes, max_slots):
+    """The slot schedule of the fluid part of a step (csrc/gas_schedule.cpp, found by search) must be a re-ordering that no cell can
+    notice: every operation of the reference's sequence (PistonEngineSimulator::simulateStep_, archive/TA2_FINDINGS.md:194-199) exactly
+    once, no two operations of a slot on one cell, each cell's own operations in the reference's order.  The library checks that itself
+    (EsbGasScheduleInfo); here for every golden engine and several lane counts, with the slot counts the search is expected to reach."""
+    from engine_sim_cli_b200 import api
+    _lib_path()
+    blob = open(os.path.join(GOLDEN, engine + ".params.bin"), "rb").read()
+    info = api.gas_schedule_info(blob, min_lanes=lanes)
+    assert info["rc"] == 0 and info["problem"] == "", info
+    assert info["lanes"] >= lanes
+    if max_slots:
+        assert info["exchange_slots"] <= max_slots[0] and info["relax_slots"] <= max_slots[1], info
+    # other substep counts go through the same search
+    info4 = api.gas_schedule_info(blob, min_lanes=lanes, fluid_steps=4)
+    assert info4["rc"] == 0 and info4["problem"] == "", info4
+    assert info4["exchange_slots"] < info["exchange_slots"]
