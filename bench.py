@@ -431,10 +431,10 @@ def main():
                 "avg_launch_ms": phys_ms / phys_n, "launches_timed": phys_n, "share_of_step": phys_ms / r["ms_total"]}
     # DRAM bytes of one launch from the committed ncu --set full capture of the SAME launch shape (no scaling: the state load / store
     # happens once per launch whatever its length); null when the shapes differ
-    prof = load_json(os.path.join(ROOT, "profiles", "physics_ncu_r02e.json"))
+    prof = load_json(os.path.join(ROOT, "profiles", "physics_ncu_r02f.json"))
     if prof and "dram_bytes_per_launch" in prof and prof.get("steps_in_launch") == per_launch_steps and prof.get("instances") == n and args.engine == "gm_ls":
         roofline["traffic"] = prof["dram_bytes_per_launch"]
-        roofline["traffic_source"] = "profiles/physics_ncu_r02e.json (dram__bytes_read.sum + dram__bytes_write.sum of one %d-step launch)" % prof["steps_in_launch"]
+        roofline["traffic_source"] = "profiles/physics_ncu_r02f.json (dram__bytes_read.sum + dram__bytes_write.sum of one %d-step launch)" % prof["steps_in_launch"]
     # secondary lines: convolution against the FP32 pipe, buffer streams against HBM
     L = r["taps"][0]
     samples_total = args.steps * (r["b"].samples_for(steps))
