@@ -15,6 +15,7 @@ FP64 = ("DFMA", "DMUL", "DADD", "DSETP")
 
 
 def disassemble(so):
+    so = os.path.abspath(so)
     with tempfile.TemporaryDirectory() as d:
         subprocess.run(["cuobjdump", "-xelf", "physics_kernel", so], cwd=d, check=True, capture_output=True)
         cubin = [f for f in os.listdir(d) if f.endswith(".cubin")][0]
@@ -28,7 +29,12 @@ def functions(txt):
     end = [i for i, l in enumerate(txt) if l.startswith(".text.") and i > start][0]
     seg, cur, name = [], [], "kernel body"
     for l in txt[start:end]:
-        m = re.match(r"^\$.*?4esbk\d+([A-Za-z_0-9]+?)E[PdRKiv]", l) or re.match(r"^\$__internal_\d+_\$(\w+):", l)
+        m = re.match(r"^\$_ZN4esbk18esb_physics_kernel.*?\$_ZN\d+_INTERNAL_\w+?4esbk(\d+)([A-Za-z0-9_]+)", l)
+        if m and l.rstrip().endswith(":"):
+            seg.append((name, cur))
+            cur, name = [], m.group(2)[:int(m.group(1))]
+            continue
+        m = re.match(r"^\$__internal_\d+_\$(\w+):", l)
         if m:
             seg.append((name, cur))
             cur, name = [], m.group(1)
@@ -93,6 +99,10 @@ def main():
     arg = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "engine-sim-cli_b200", "libenginesim_b200.so")
     txt = open(arg).read() if arg.endswith(".sass") else disassemble(arg)
     for name, fn in functions(txt):
+        # the fast path of an out-of-line function: up to its first return (slow-path tails and the divergent forms of the shuffles follow it)
+        ret = [i for i, ins in enumerate(fn) if ins.startswith("RET")]
+        if ret and name != "kernel body":
+            fn = fn[:ret[0] + 1]
         if len(fn) >= 300 and name != "kernel body":
             cyc = model(fn)
             nfp = sum(1 for i in fn if (i.split()[1] if i.startswith("@") else i.split()[0]).split(".")[0] in FP64)
